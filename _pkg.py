@@ -1,0 +1,20 @@
+"""Import the package directory `c-raytracer_b200/` under the importable name
+`c_raytracer_b200` (a hyphen is not valid in a module name)."""
+import importlib.util
+import os
+import sys
+
+_NAME = "c_raytracer_b200"
+
+
+def load():
+    if _NAME in sys.modules:
+        return sys.modules[_NAME]
+    root = os.path.dirname(os.path.abspath(__file__))
+    pkg_dir = os.path.join(root, "c-raytracer_b200")
+    spec = importlib.util.spec_from_file_location(
+        _NAME, os.path.join(pkg_dir, "__init__.py"), submodule_search_locations=[pkg_dir])
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[_NAME] = mod
+    spec.loader.exec_module(mod)
+    return mod

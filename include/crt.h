@@ -1,0 +1,257 @@
+/*
+ * crt.h -- C ABI of the B200 trace-loop library (libcrt.so).
+ *
+ * This is the drop-in boundary for the per-pixel trace loop of
+ * wojciech-graj/C-Raytracer.  The reference has no plugin / FFI interface:
+ * the seam is `void render(void)` over file-scope globals
+ * (reference src/raytracer/render.h:17-18, called from main.c:77-79), with the
+ * two finer seams `get_closest_intersection()` and `is_light_blocked()`
+ * (reference src/raytracer/render.c:48-49, :118-134).  Every entry point below
+ * names the reference interface it replaces.
+ *
+ * Plain C, plain pointers and sizes; no C++/torch types.  All functions return
+ * CRT_OK (0) or a negative error code; crt_last_error() gives the message.
+ * No function calls exit(); the C host (src/raytracer) turns a non-zero return
+ * into the reference's `error()` behaviour (reference src/core/error.h:21-26).
+ *
+ * There is NO CPU fallback behind this ABI: if no CUDA device is usable every
+ * compute entry point fails with CRT_ERR_NO_DEVICE.
+ */
+#ifndef CRT_H
+#define CRT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CRT_ABI_VERSION 1
+
+enum crt_status {
+	CRT_OK = 0,
+	CRT_ERR_INVALID = -1,   /* bad argument / malformed scene description */
+	CRT_ERR_NO_DEVICE = -2, /* no usable CUDA device */
+	CRT_ERR_CUDA = -3,      /* CUDA runtime error, see crt_last_error() */
+	CRT_ERR_NOMEM = -4,
+	CRT_ERR_UNSUPPORTED = -5,
+};
+
+/* Object kinds: reference `enum ObjectType` (src/raytracer/object.h:18-24). */
+enum crt_object_type {
+	CRT_OBJ_SPHERE = 0,
+	CRT_OBJ_TRIANGLE = 1,
+	CRT_OBJ_PLANE = 2,
+};
+
+/* Texture kinds: the four `texture_get_color_*` (src/raytracer/material.c:152-200). */
+enum crt_texture_type {
+	CRT_TEX_UNIFORM = 0,
+	CRT_TEX_CHECKERBOARD = 1,
+	CRT_TEX_BRICK = 2,
+	CRT_TEX_NOISY_PERIODIC = 3,
+};
+
+/* reference `enum PeriodicFunction` (src/raytracer/material.h:17-22) */
+enum crt_periodic_func {
+	CRT_FUNC_SIN = 0,
+	CRT_FUNC_SAW = 1,
+	CRT_FUNC_TRIANGLE = 2,
+	CRT_FUNC_SQUARE = 3,
+};
+
+/* material flags, derived exactly as reference material.c:81-83 (|k| > 1e-6) */
+#define CRT_MAT_REFLECTIVE 1u
+#define CRT_MAT_TRANSPARENT 2u
+#define CRT_MAT_EMITTANT 4u
+
+/*
+ * One material with its (single) procedural texture.
+ * Replaces `struct Material` (material.h:31-44) + the texture structs
+ * (material.c:27-53).  128 bytes.
+ *
+ * Texture parameter mapping:
+ *   uniform        : color[0]
+ *   checkerboard   : color[0], color[1], scale
+ *   brick          : color[0], color[1], scale, param1 = mortar width
+ *   noisy periodic : color[0] = color, color[1] = colour gradient,
+ *                    scale = noise feature scale, param1 = noise scale,
+ *                    param2 = frequency scale, tex_func = crt_periodic_func
+ */
+typedef struct crt_material {
+	float ks[3];
+	float ka[3];
+	float kr[3];
+	float kt[3];
+	float ke[3];
+	float shininess;
+	float refractive_index;
+	uint32_t flags;   /* CRT_MAT_* ; recomputed by crt_scene_create if 0xffffffff */
+	int32_t tex_type; /* crt_texture_type */
+	int32_t tex_func; /* crt_periodic_func */
+	float color[2][3];
+	float scale;
+	float param1;
+	float param2;
+	int32_t id;       /* scene-file id, informational */
+	float reserved[2];
+} crt_material;
+
+/*
+ * One scene object, in SCENE ORDER (the order of the reference's `objects[]`,
+ * object.h:79: JSON order, with each mesh expanded in place into its
+ * triangles, scene.c:329-360 / object.c:542-587).  Order matters: it defines
+ * emitter order (render.c:170), plane order and the RNG draw order.  64 bytes.
+ *
+ *   sphere   : a = centre, b[0] = radius                     (object.c:24-28)
+ *   triangle : a = vertex 0, b = edge v1-v0, c = edge v2-v0,
+ *              n = unit normal normalize(b x c)              (object.c:30-35, :327-334)
+ *   plane    : a = unit normal, b[0] = d  (a.x = d)          (object.c:38-42, :457-468)
+ *
+ * epsilon is the RESOLVED value (auto rules object.c:235-236, :336-339,
+ * :453-454 already applied by the loader).
+ */
+typedef struct crt_object {
+	int32_t type;        /* crt_object_type */
+	int32_t material;    /* index into crt_scene_desc.materials (not the JSON id) */
+	uint32_t num_lights; /* shadow samples when this object is an emitter (scene.c:373) */
+	float epsilon;
+	float a[3];
+	float b[3];
+	float c[3];
+	float n[3];
+} crt_object;
+
+/*
+ * The scene as flat host arrays: everything `render()` reads from globals
+ * (objects/num_objects object.h:79-86, materials material.h:59-60,
+ * global_ambient_light_intensity render.h:20).  Caller-owned, only read during
+ * crt_scene_create().
+ */
+typedef struct crt_scene_desc {
+	uint32_t abi_version; /* CRT_ABI_VERSION */
+	uint32_t num_objects;
+	const crt_object *objects;
+	uint32_t num_materials;
+	const crt_material *materials;
+	float ambient[3]; /* "AmbientLight", scene.c:104-105 */
+	float reserved;
+} crt_scene_desc;
+
+enum crt_reflection_model { CRT_REFLECTION_PHONG = 0, CRT_REFLECTION_BLINN = 1 };
+enum crt_gi_model { CRT_GI_AMBIENT = 0, CRT_GI_PATH = 1 };
+enum crt_attenuation { CRT_ATTEN_NONE = 0, CRT_ATTEN_LINEAR = 1, CRT_ATTEN_SQUARE = 2 };
+
+#define CRT_RENDER_COUNT_STATS 1u /* run the instrumented kernel (ray / test counters) */
+
+/*
+ * Per-frame parameters: the image plane `struct Image` (image.h:17-26, set up
+ * by image_init image.c:34-56), `camera.position` (camera.h:17-22) and the
+ * render statics (render.c:52-59, parsed by render_init :61-116).
+ */
+typedef struct crt_render_opts {
+	uint32_t width, height;
+	float cam_pos[3];
+	float corner[3]; /* image.corner */
+	float vx[3];     /* image.vectors[X] */
+	float vy[3];     /* image.vectors[Y] */
+	uint32_t max_bounces;      /* -b, default 10 */
+	float min_intensity_sqr;   /* (-a)^2, default 1e-4 */
+	int32_t reflection_model;  /* -s */
+	int32_t gi_model;          /* -g */
+	uint32_t samples_per_pixel;/* -n */
+	int32_t attenuation;       /* -l */
+	float attenuation_offset;  /* -o, default 1 */
+	uint32_t seed;             /* counter-based RNG seed (include/crt_rng.h) */
+	uint32_t flags;            /* CRT_RENDER_* */
+	/* Multi-GPU sharding: tile-chunk k is rendered iff k % shard_count ==
+	 * shard_index.  Pixels of other shards are left zero.  (1-rank: 0 / 1.) */
+	uint32_t shard_index, shard_count;
+	uint32_t reserved[4];
+} crt_render_opts;
+
+/* Counters of one crt_render call (all zero unless CRT_RENDER_COUNT_STATS). */
+typedef struct crt_stats {
+	uint64_t rays_closest; /* get_closest_intersection calls incl. inside-object shortcut */
+	uint64_t rays_shadow;  /* is_light_blocked calls */
+	uint64_t box_tests;    /* ray/AABB slab tests */
+	uint64_t tri_tests[4]; /* Moeller-Trumbore tests by exit stage: parallel / u / v / complete */
+	uint64_t sphere_tests[2]; /* miss / hit */
+	uint64_t plane_tests;
+	uint64_t nodes_shaded; /* cast_ray invocations that found a hit */
+	double kernel_ms;      /* device time of the trace kernel(s), CUDA events */
+	double total_ms;       /* wall time of the call incl. copies */
+	uint64_t reserved[4];
+} crt_stats;
+
+typedef struct crt_scene crt_scene; /* opaque; owns all device memory */
+
+/* Information about the built acceleration structure. */
+typedef struct crt_scene_info {
+	uint32_t num_bounded; /* spheres + triangles (BVH leaves' primitives) */
+	uint32_t num_planes;
+	uint32_t num_emitters;
+	uint32_t total_lights; /* sum of num_lights over emitters */
+	uint32_t num_nodes;    /* BVH nodes (two child boxes per 64-byte node) */
+	uint32_t max_depth;
+	uint32_t device;       /* CUDA device ordinal */
+	uint32_t sm_count;
+	double build_ms;       /* host BVH build */
+	double upload_ms;
+	uint64_t device_bytes;
+} crt_scene_info;
+
+const char *crt_last_error(void);
+int crt_abi_version(void);
+int crt_device_count(void);
+
+/* Build the BVH, flatten and upload the scene to CUDA device `device`.
+ * Replaces accel_init() (accel.c:266-315) plus the globals hand-off. */
+int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out);
+void crt_scene_destroy(crt_scene *scene);
+int crt_scene_get_info(const crt_scene *scene, crt_scene_info *info);
+
+/* Replaces render() (render.c:345-368).  raster = W*H*3 floats, z_buffer =
+ * W*H floats, HOST memory, row-major top-left origin, fully overwritten
+ * (zero where nothing was hit: reference relies on fresh zero pages,
+ * image.c:45-46).  stats may be NULL. */
+int crt_render(crt_scene *scene, const crt_render_opts *opts,
+	float *raster, float *z_buffer, crt_stats *stats);
+
+/* Same, but raster / z_buffer are DEVICE pointers on the scene's device and the
+ * work is enqueued on `cuda_stream` (a cudaStream_t, may be NULL for the
+ * default stream) without synchronising.  stats (may be NULL) is filled only
+ * by crt_render_device_sync(). */
+int crt_render_device(crt_scene *scene, const crt_render_opts *opts,
+	float *d_raster, float *d_z_buffer, void *cuda_stream);
+int crt_render_device_sync(crt_scene *scene, crt_stats *stats);
+
+/* Ray-batch seams (tests, tools).  rays = n * 6 floats: direction xyz then
+ * point xyz, the layout of `struct Ray` (object.h:27-30).
+ * crt_trace_closest replaces get_closest_intersection() (render.c:118-124):
+ *   object[i] = scene-order object index or -1, t[i] = distance (FLT_MAX on
+ *   miss), normal = n*3 floats (may be NULL).
+ * crt_trace_shadow replaces is_light_blocked() (render.c:126-134):
+ *   light = n*3 floats in/out (multiplied by kt of every transparent occluder),
+ *   emitter[i] = scene-order object index of the sampled emitter (or -1),
+ *   blocked[i] = 1 if an opaque occluder lies within dist[i]. */
+int crt_trace_closest(crt_scene *scene, const float *rays, size_t n,
+	int32_t *object, float *t, float *normal);
+int crt_trace_shadow(crt_scene *scene, const float *rays, const float *dist,
+	const int32_t *emitter, size_t n, float *light, uint8_t *blocked);
+
+/* Evaluate material `material`'s texture at n points (n*3 floats) -> n*3
+ * colours.  Replaces Texture.get_color (material.h:27-29). */
+int crt_texture_eval(crt_scene *scene, int32_t material, const float *points,
+	size_t n, float *colors);
+
+/* FP32 FMA micro-benchmark on the scene's device: measured TFLOP/s, the
+ * denominator of the ray-test roofline. */
+int crt_measure_fp32_peak(int device, double *tflops);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* CRT_H */

@@ -1,0 +1,114 @@
+/*
+ * main.c -- the `engine` executable: same command line, log lines, scene
+ * files and output files as the reference engine (reference
+ * src/raytracer/main.c:23-89), with the trace loop running on a B200 through
+ * include/crt.h.
+ */
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "argv.h"
+#include "error.h"
+#include "image.h"
+#include "render.h"
+#include "scene.h"
+#include "system.h"
+
+static const char *const HELP_TEXT =
+	"Render a scene using raytracing.\n"
+	"Copyright: (c) 2021-2022 Wojciech Graj\n"
+	"License: https://opensource.org/licenses/MIT\n"
+	"Features: Multithreading Planes \n"
+	"Usage: ./engine <input> <output> <resolution> [OPTIONAL_PARAMETERS]\n"
+	"\n"
+	"REQUIRED PARAMETERS:\n"
+	"<input>      (string)            : .json scene file which will be used to generate the image. Example files can be found in ./scenes.\n"
+	"<output>     (string)            : .tif file to which the image will be saved.\n"
+	"<resolution> (integer) (integer) : resolution of the output image.\n"
+	"OPTIONAL PARAMETERS:\n"
+	"[-m] (integer | \"max\")           : DEFAULT = 1       : number of CPU cores\n"
+	"[-b] (integer)                   : DEFAULT = 10      : maximum number of times that a light ray can bounce.\n"
+	"[-a] (float)                     : DEFAULT = 0.01    : minimum light intensity for which a ray is cast.\n"
+	"[-s] (\"phong\" | \"blinn\")         : DEFAULT = phong   : reflection model.\n"
+	"[-n] (integer)                   : DEFAULT = 1       : number of samples which are rendered per pixel.\n"
+	"[-r] (\"norm\" | float)            : DEFAULT = 1.0     : scene scaling factor.\n"
+	"[-l] (\"none\" | \"lin\" | \"sqr\")    : DEFAULT = sqr     : light attenuation.\n"
+	"[-p] (\"real\" | \"cpu\")            : DEFAULT = real    : time to print with status messages.\n"
+	"[-g] (string)                    : DEFAULT = ambient : global illumination model.\n"
+	"    ambient    : ambient lighting\n"
+	"    path       : path-tracing\n"
+	"[-f]                             : DEFAULT = OFF     : save raw output for post-processing.\n";
+
+static const char *const HELP_EXTRA =
+	"B200 BUILD, ADDITIONAL PARAMETERS:\n"
+	"[--device] (integer)             : DEFAULT = 0       : CUDA device the trace loop runs on ([-m] is accepted and ignored).\n"
+	"[--seed] (integer)               : DEFAULT = 1       : seed of the counter-based sampling stream.\n"
+	"[--stats]                        : DEFAULT = OFF     : count rays and intersection tests, print Mrays/s.\n";
+
+int main(int argc, char *argv[])
+{
+	struct rt_args args;
+	if (rt_args_init(&args, argc, argv))
+		return 1;
+
+	if (rt_args_find(&args, "--help") || rt_args_find(&args, "-h")) {
+		puts(HELP_TEXT);
+		puts(HELP_EXTRA);
+		return 0;
+	}
+	if (argc < 5) {
+		puts("Too few arguments. Use --help to find out which arguments are required to call this program.");
+		return 1;
+	}
+
+	rt_system_init(&args);
+	char err[RT_ERRLEN] = "";
+
+	rt_log("Loading scene.");
+	struct rt_scene scene;
+	const int r = rt_args_find_with_values(&args, "-r", 1);
+	if (rt_scene_load(argv[RT_ARG_SCENE], r ? argv[r + 1] : NULL, &scene, err))
+		rt_fatal("%s", err);
+	rt_log("Loaded %zu materials, %zu objects.", scene.num_materials, scene.num_objects);
+
+	rt_log("Initializing image.");
+	struct rt_image image;
+	rt_image_plane(&image, &scene.camera, (uint32_t)abs(atoi(argv[RT_ARG_WIDTH])), (uint32_t)abs(atoi(argv[RT_ARG_HEIGHT])));
+	if (rt_image_alloc(&image, err))
+		rt_fatal("%s", err);
+
+	crt_render_opts opts;
+	rt_render_defaults(&opts);
+	rt_render_parse(&opts, &args);
+	rt_render_set_view(&opts, &scene, &image);
+	const int d = rt_args_find_with_values(&args, "--device", 1);
+	const int device = d ? atoi(argv[d + 1]) : 0;
+
+	rt_log("Commencing raytracing.");
+	crt_stats stats;
+	crt_scene_info info;
+	if (rt_render(&scene, &image, &opts, device, &stats, &info, err))
+		rt_fatal("%s", err);
+	rt_log("BVH: %u nodes over %u primitives, depth %u, built in %.1f ms; trace kernel %.3f ms, call %.3f ms.",
+		info.num_nodes, info.num_bounded, info.max_depth, info.build_ms, stats.kernel_ms, stats.total_ms);
+	if (opts.flags & CRT_RENDER_COUNT_STATS) {
+		const double rays = (double)(stats.rays_closest + stats.rays_shadow);
+		rt_log("Rays: %llu closest-hit + %llu shadow = %.1f Mrays/s; %.1f box tests per ray.",
+			(unsigned long long)stats.rays_closest, (unsigned long long)stats.rays_shadow,
+			rays / (stats.kernel_ms * 1e3), rays > 0 ? (double)stats.box_tests / rays : 0.0);
+	}
+
+	rt_log("Saving image.");
+	const char *out = argv[RT_ARG_OUTPUT];
+	if (!strstr(out, ".tif"))
+		rt_log("Expected output file [%s] with extension .tif.", out);
+	if (rt_image_save(&image, out, rt_args_find(&args, "-f") != 0, err))
+		rt_fatal("%s", err);
+
+	rt_log("Terminating.");
+	rt_image_free(&image);
+	rt_scene_free(&scene);
+	rt_args_free(&args);
+	return 0;
+}
