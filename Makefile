@@ -11,7 +11,7 @@ HOST_SRCS := src/core/argv.c src/core/strhash.c src/core/system.c \
 	src/raytracer/camera.c src/raytracer/material.c src/raytracer/object.c src/raytracer/scene.c \
 	src/raytracer/image.c src/raytracer/tiff.c src/raytracer/options.c src/raytracer/hostapi.c lib/json/json.c
 CSRC := c-raytracer_b200/csrc
-NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 --use_fast_math=false \
+NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 \
 	-Xcompiler -fPIC -Iinclude -I$(CSRC)
 DEVICE_SRCS := $(CSRC)/crt_api.cu $(CSRC)/crt_kernels.cu $(CSRC)/bvh_build.cpp
 

@@ -1,0 +1,227 @@
+/*
+ * bvh_build.cpp -- binned-SAH BVH builder (host).  See bvh_build.h.
+ */
+#include "bvh_build.h"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+namespace crt {
+
+namespace {
+
+constexpr int kBins = 16;
+constexpr float kTraversalCost = 1.2f; /* relative to one primitive test */
+constexpr uint32_t kMedianDepth = 40;  /* below this depth: median splits only, bounds the device stack */
+
+struct Builder {
+	const std::vector<Aabb> &boxes;
+	std::vector<float> centroid; /* 3 per box */
+	std::vector<uint32_t> &order;
+	std::vector<BvhNode> &nodes;
+	uint32_t max_depth = 0;
+
+	Builder(const std::vector<Aabb> &b, BvhResult &out) : boxes(b), order(out.order), nodes(out.nodes) {}
+};
+
+inline void box_reset(Aabb &b)
+{
+	for (int k = 0; k < 3; k++) {
+		b.lo[k] = FLT_MAX;
+		b.hi[k] = -FLT_MAX;
+	}
+}
+
+inline void box_grow(Aabb &b, const Aabb &o)
+{
+	for (int k = 0; k < 3; k++) {
+		b.lo[k] = std::min(b.lo[k], o.lo[k]);
+		b.hi[k] = std::max(b.hi[k], o.hi[k]);
+	}
+}
+
+inline float half_area(const Aabb &b)
+{
+	const float dx = b.hi[0] - b.lo[0], dy = b.hi[1] - b.lo[1], dz = b.hi[2] - b.lo[2];
+	if (dx < 0.f || dy < 0.f || dz < 0.f)
+		return 0.f;
+	return dx * dy + dy * dz + dz * dx;
+}
+
+inline int32_t encode_leaf(uint32_t first, uint32_t count)
+{
+	return ~static_cast<int32_t>((first << kLeafCountBits) | (count - 1u));
+}
+
+void store_child(BvhNode &n, int which, int32_t ref, const Aabb &b)
+{
+	float *xy = which == 0 ? n.xy0 : n.xy1;
+	xy[0] = b.lo[0];
+	xy[1] = b.hi[0];
+	xy[2] = b.lo[1];
+	xy[3] = b.hi[1];
+	n.z01[2 * which + 0] = b.lo[2];
+	n.z01[2 * which + 1] = b.hi[2];
+	n.child[which] = ref;
+}
+
+/* Builds the subtree over order[first, first+count); returns the child
+ * reference (node index or encoded leaf) and its bounds. */
+int32_t build_range(Builder &B, uint32_t first, uint32_t count, uint32_t depth, Aabb &bounds)
+{
+	B.max_depth = std::max(B.max_depth, depth);
+	box_reset(bounds);
+	Aabb cbox;
+	box_reset(cbox);
+	for (uint32_t i = first; i < first + count; i++) {
+		const uint32_t p = B.order[i];
+		box_grow(bounds, B.boxes[p]);
+		for (int k = 0; k < 3; k++) {
+			cbox.lo[k] = std::min(cbox.lo[k], B.centroid[3 * p + k]);
+			cbox.hi[k] = std::max(cbox.hi[k], B.centroid[3 * p + k]);
+		}
+	}
+	if (count == 1)
+		return encode_leaf(first, 1);
+
+	/* --- choose a split ------------------------------------------------ */
+	int best_axis = -1, best_bin = -1;
+	float best_cost = FLT_MAX;
+	const float parent_area = half_area(bounds);
+	if (depth < kMedianDepth && parent_area > 0.f) {
+		for (int axis = 0; axis < 3; axis++) {
+			const float extent = cbox.hi[axis] - cbox.lo[axis];
+			if (!(extent > 0.f))
+				continue;
+			Aabb bin_box[kBins];
+			uint32_t bin_count[kBins];
+			for (int b = 0; b < kBins; b++) {
+				box_reset(bin_box[b]);
+				bin_count[b] = 0;
+			}
+			const float scale = kBins / extent;
+			for (uint32_t i = first; i < first + count; i++) {
+				const uint32_t p = B.order[i];
+				int b = static_cast<int>((B.centroid[3 * p + axis] - cbox.lo[axis]) * scale);
+				b = std::min(std::max(b, 0), kBins - 1);
+				bin_count[b]++;
+				box_grow(bin_box[b], B.boxes[p]);
+			}
+			float right_area[kBins];
+			uint32_t right_count[kBins];
+			Aabb acc;
+			box_reset(acc);
+			uint32_t n = 0;
+			for (int b = kBins - 1; b > 0; b--) {
+				box_grow(acc, bin_box[b]);
+				n += bin_count[b];
+				right_area[b] = half_area(acc);
+				right_count[b] = n;
+			}
+			box_reset(acc);
+			n = 0;
+			for (int b = 0; b < kBins - 1; b++) {
+				box_grow(acc, bin_box[b]);
+				n += bin_count[b];
+				if (n == 0 || right_count[b + 1] == 0)
+					continue;
+				const float cost = half_area(acc) * n + right_area[b + 1] * right_count[b + 1];
+				if (cost < best_cost) {
+					best_cost = cost;
+					best_axis = axis;
+					best_bin = b;
+				}
+			}
+		}
+	}
+
+	if (best_axis >= 0 && count <= static_cast<uint32_t>(kMaxLeafPrims)) {
+		const float split_cost = kTraversalCost + best_cost / parent_area;
+		if (split_cost >= static_cast<float>(count))
+			return encode_leaf(first, count);
+	}
+
+	uint32_t mid;
+	if (best_axis >= 0) {
+		const float lo = cbox.lo[best_axis];
+		const float scale = kBins / (cbox.hi[best_axis] - lo);
+		uint32_t *begin = B.order.data() + first;
+		uint32_t *split = std::partition(begin, begin + count, [&](uint32_t p) {
+			int b = static_cast<int>((B.centroid[3 * p + best_axis] - lo) * scale);
+			b = std::min(std::max(b, 0), kBins - 1);
+			return b <= best_bin;
+		});
+		mid = static_cast<uint32_t>(split - begin);
+	} else {
+		mid = 0;
+	}
+	if (mid == 0 || mid == count) {
+		/* binning failed (coincident centroids) or forced: median split on the widest axis */
+		if (count <= static_cast<uint32_t>(kMaxLeafPrims) && best_axis < 0 && depth < kMedianDepth)
+			return encode_leaf(first, count);
+		int axis = 0;
+		for (int k = 1; k < 3; k++)
+			if (cbox.hi[k] - cbox.lo[k] > cbox.hi[axis] - cbox.lo[axis])
+				axis = k;
+		mid = count / 2;
+		uint32_t *begin = B.order.data() + first;
+		std::nth_element(begin, begin + mid, begin + count, [&](uint32_t a, uint32_t b) {
+			const float ca = B.centroid[3 * a + axis], cb = B.centroid[3 * b + axis];
+			return ca < cb || (ca == cb && a < b);
+		});
+		if (count <= static_cast<uint32_t>(kMaxLeafPrims) && depth >= kMedianDepth)
+			return encode_leaf(first, count);
+	}
+
+	const int32_t id = static_cast<int32_t>(B.nodes.size());
+	B.nodes.emplace_back();
+	std::memset(&B.nodes[id], 0, sizeof(BvhNode));
+	Aabb lb, rb;
+	const int32_t l = build_range(B, first, mid, depth + 1, lb);
+	const int32_t r = build_range(B, first + mid, count - mid, depth + 1, rb);
+	store_child(B.nodes[id], 0, l, lb);
+	store_child(B.nodes[id], 1, r, rb);
+	return id;
+}
+
+} // namespace
+
+void build_bvh(const std::vector<Aabb> &boxes, BvhResult &out)
+{
+	out.nodes.clear();
+	out.order.clear();
+	out.max_depth = 0;
+	const uint32_t n = static_cast<uint32_t>(boxes.size());
+	if (n == 0)
+		return;
+	out.order.resize(n);
+	for (uint32_t i = 0; i < n; i++)
+		out.order[i] = i;
+	Builder B(boxes, out);
+	B.centroid.resize(3 * static_cast<size_t>(n));
+	for (uint32_t i = 0; i < n; i++)
+		for (int k = 0; k < 3; k++)
+			B.centroid[3 * i + k] = 0.5f * (boxes[i].lo[k] + boxes[i].hi[k]);
+	out.nodes.reserve(n);
+
+	Aabb root_box;
+	const int32_t root = build_range(B, 0, n, 1, root_box);
+	if (root < 0) {
+		/* the whole scene fits one leaf: wrap it so that node 0 is an inner node */
+		BvhNode node;
+		std::memset(&node, 0, sizeof node);
+		Aabb empty;
+		for (int k = 0; k < 3; k++) {
+			empty.lo[k] = FLT_MAX;
+			empty.hi[k] = -FLT_MAX;
+		}
+		store_child(node, 0, root, root_box);
+		store_child(node, 1, encode_leaf(0, 1), empty);
+		out.nodes.push_back(node);
+	}
+	out.max_depth = B.max_depth;
+}
+
+} // namespace crt

@@ -1,0 +1,582 @@
+/*
+ * crt_api.cu -- implementation of the C ABI in include/crt.h on top of the
+ * kernels in crt_kernels.cu.  No CPU fallback: without a CUDA device every
+ * compute entry point fails with CRT_ERR_NO_DEVICE.
+ */
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "bvh_build.h"
+#include "crt_kernels.cuh"
+
+using namespace crt;
+
+namespace {
+
+thread_local char g_error[512] = "";
+
+int fail(int code, const char *fmt, ...)
+{
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_error, sizeof g_error, fmt, ap);
+	va_end(ap);
+	return code;
+}
+
+#define CUDA_TRY(expr)                                                                          \
+	do {                                                                                    \
+		cudaError_t e_ = (expr);                                                        \
+		if (e_ != cudaSuccess)                                                          \
+			return fail(CRT_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_)); \
+	} while (0)
+
+double now_ms()
+{
+	using namespace std::chrono;
+	return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+float as_float(uint32_t u)
+{
+	float f;
+	std::memcpy(&f, &u, 4);
+	return f;
+}
+
+} // namespace
+
+struct crt_scene {
+	int device = 0;
+	int sm_count = 0;
+	DScene d{};
+	crt_scene_info info{};
+	std::vector<void *> allocs;
+	std::vector<int32_t> slot_object; /* host copy: prim slot -> scene object (for the ray-batch seams) */
+	/* per-frame scratch, grown on demand */
+	float *row_pos = nullptr;
+	size_t row_pos_floats = 0;
+	float *pending = nullptr;
+	size_t pending_floats = 0;
+	unsigned int *tile_counter = nullptr;
+	unsigned long long *counters = nullptr;
+	float *d_raster = nullptr, *d_z = nullptr; /* staging for crt_render (host buffers) */
+	size_t staging_pixels = 0;
+	cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+	cudaStream_t last_stream = nullptr;
+	bool frame_pending = false;
+	bool frame_counted = false;
+};
+
+namespace {
+
+template <typename T>
+int upload(crt_scene *s, const std::vector<T> &host, const T **dev)
+{
+	*dev = nullptr;
+	if (host.empty())
+		return CRT_OK;
+	void *p = nullptr;
+	CUDA_TRY(cudaMalloc(&p, host.size() * sizeof(T)));
+	s->allocs.push_back(p);
+	s->info.device_bytes += host.size() * sizeof(T);
+	CUDA_TRY(cudaMemcpy(p, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice));
+	*dev = static_cast<const T *>(p);
+	return CRT_OK;
+}
+
+int validate(const crt_scene_desc *desc)
+{
+	if (!desc)
+		return fail(CRT_ERR_INVALID, "scene description is NULL");
+	if (desc->abi_version != CRT_ABI_VERSION)
+		return fail(CRT_ERR_INVALID, "ABI version mismatch: caller %u, library %d", desc->abi_version, CRT_ABI_VERSION);
+	if (!desc->num_objects || !desc->objects)
+		return fail(CRT_ERR_INVALID, "scene has no objects");
+	if (!desc->num_materials || !desc->materials)
+		return fail(CRT_ERR_INVALID, "scene has no materials");
+	if (desc->num_materials > PRIM_MATERIAL_MASK)
+		return fail(CRT_ERR_INVALID, "too many materials");
+	for (uint32_t i = 0; i < desc->num_objects; i++) {
+		const crt_object &o = desc->objects[i];
+		if (o.type != CRT_OBJ_SPHERE && o.type != CRT_OBJ_TRIANGLE && o.type != CRT_OBJ_PLANE)
+			return fail(CRT_ERR_INVALID, "object %u has unknown type %d", i, o.type);
+		if (o.material < 0 || static_cast<uint32_t>(o.material) >= desc->num_materials)
+			return fail(CRT_ERR_INVALID, "object %u references material index %d of %u", i, o.material, desc->num_materials);
+	}
+	return CRT_OK;
+}
+
+uint32_t material_flags(const crt_material &m)
+{
+	if (m.flags != 0xffffffffu)
+		return m.flags;
+	auto mag = [](const float *k) { return std::sqrt(k[0] * k[0] + k[1] * k[1] + k[2] * k[2]); };
+	return (mag(m.kr) > 1e-6f ? CRT_MAT_REFLECTIVE : 0u) | (mag(m.kt) > 1e-6f ? CRT_MAT_TRANSPARENT : 0u) |
+		(mag(m.ke) > 1e-6f ? CRT_MAT_EMITTANT : 0u);
+}
+
+int ensure_device(int device)
+{
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) {
+		cudaGetLastError();
+		return fail(CRT_ERR_NO_DEVICE, "no CUDA device available (this library has no CPU fallback)");
+	}
+	if (device < 0 || device >= n)
+		return fail(CRT_ERR_INVALID, "device %d out of range (%d devices)", device, n);
+	CUDA_TRY(cudaSetDevice(device));
+	return CRT_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *crt_last_error(void)
+{
+	return g_error;
+}
+
+int crt_abi_version(void)
+{
+	return CRT_ABI_VERSION;
+}
+
+int crt_device_count(void)
+{
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess) {
+		cudaGetLastError();
+		return 0;
+	}
+	return n;
+}
+
+void crt_scene_destroy(crt_scene *s)
+{
+	if (!s)
+		return;
+	cudaSetDevice(s->device);
+	for (void *p : s->allocs)
+		cudaFree(p);
+	cudaFree(s->row_pos);
+	cudaFree(s->pending);
+	cudaFree(s->tile_counter);
+	cudaFree(s->counters);
+	cudaFree(s->d_raster);
+	cudaFree(s->d_z);
+	if (s->ev_start)
+		cudaEventDestroy(s->ev_start);
+	if (s->ev_stop)
+		cudaEventDestroy(s->ev_stop);
+	delete s;
+}
+
+int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
+{
+	if (!out)
+		return fail(CRT_ERR_INVALID, "out is NULL");
+	*out = nullptr;
+	int rc = validate(desc);
+	if (rc)
+		return rc;
+	rc = ensure_device(device);
+	if (rc)
+		return rc;
+
+	crt_scene *s = new crt_scene();
+	s->device = device;
+	cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
+
+	/* ---- materials ------------------------------------------------------ */
+	std::vector<crt_material> mats(desc->materials, desc->materials + desc->num_materials);
+	for (auto &m : mats)
+		m.flags = material_flags(m);
+
+	/* ---- split objects: planes (linear list, object.c:168-197) / bounded --- */
+	const uint32_t n = desc->num_objects;
+	std::vector<uint32_t> bounded;
+	std::vector<float4> planes;
+	std::vector<int32_t> obj_slot(n, 0);
+	std::vector<DEmitter> emitters;
+	uint32_t total_lights = 0;
+	for (uint32_t i = 0; i < n; i++) {
+		const crt_object &o = desc->objects[i];
+		const crt_material &m = mats[o.material];
+		const uint32_t info = static_cast<uint32_t>(o.material) | ((m.flags & CRT_MAT_TRANSPARENT) ? PRIM_TRANSPARENT : 0u);
+		if (o.type == CRT_OBJ_PLANE) {
+			if (m.flags & CRT_MAT_EMITTANT) {
+				delete s;
+				return fail(CRT_ERR_INVALID, "Plane cannot be emittant");
+			}
+			obj_slot[i] = ~static_cast<int32_t>(planes.size() / 2);
+			planes.push_back(make_float4(o.a[0], o.a[1], o.a[2], o.b[0]));
+			planes.push_back(make_float4(o.epsilon, as_float(info), as_float(i), 0.f));
+			continue;
+		}
+		bounded.push_back(i);
+		/* emitters: bounded objects with an emittant material, in scene order
+		 * (scene.c:357-358); lights == 0 emits nothing onto others */
+		if (m.flags & CRT_MAT_EMITTANT) {
+			DEmitter e{};
+			e.object = static_cast<int32_t>(i);
+			e.num_lights = o.num_lights;
+			e.first_light = total_lights;
+			e.is_sphere = o.type == CRT_OBJ_SPHERE;
+			if (e.is_sphere) {
+				e.a = make_float4(o.a[0], o.a[1], o.a[2], o.b[0]);
+			} else {
+				e.a = make_float4(o.a[0], o.a[1], o.a[2], 0.f);
+				e.b = make_float4(o.b[0], o.b[1], o.b[2], 0.f);
+				e.c = make_float4(o.c[0], o.c[1], o.c[2], 0.f);
+			}
+			const float inv = 1.f / static_cast<float>(o.num_lights);
+			for (int k = 0; k < 3; k++)
+				e.ke_n[k] = m.ke[k] * inv;
+			total_lights += o.num_lights;
+			emitters.push_back(e);
+		}
+	}
+
+	/* ---- BVH over the bounded objects ------------------------------------- */
+	const double t0 = now_ms();
+	std::vector<Aabb> boxes(bounded.size());
+	for (size_t k = 0; k < bounded.size(); k++) {
+		const crt_object &o = desc->objects[bounded[k]];
+		Aabb &b = boxes[k];
+		for (int a = 0; a < 3; a++) {
+			if (o.type == CRT_OBJ_SPHERE) {
+				b.lo[a] = o.a[a] - o.b[0];
+				b.hi[a] = o.a[a] + o.b[0];
+			} else {
+				const float p0 = o.a[a], p1 = o.a[a] + o.b[a], p2 = o.a[a] + o.c[a];
+				b.lo[a] = std::fmin(p0, std::fmin(p1, p2));
+				b.hi[a] = std::fmax(p0, std::fmax(p1, p2));
+			}
+			/* pad by a few ulps: the slab test must never cull a true hit */
+			const float pad = 4e-7f * std::fmax(1e-3f, std::fmax(std::fabs(b.lo[a]), std::fabs(b.hi[a]))) + 1e-7f * (b.hi[a] - b.lo[a]);
+			b.lo[a] -= pad;
+			b.hi[a] += pad;
+		}
+	}
+	BvhResult bvh;
+	build_bvh(boxes, bvh);
+	s->info.build_ms = now_ms() - t0;
+
+	/* ---- primitive records in leaf order ---------------------------------- */
+	const double t1 = now_ms();
+	std::vector<float4> prims(3 * bounded.size()), normals(bounded.size());
+	s->slot_object.resize(bounded.size());
+	for (size_t slot = 0; slot < bounded.size(); slot++) {
+		const uint32_t oi = bounded[bvh.order[slot]];
+		const crt_object &o = desc->objects[oi];
+		const crt_material &m = mats[o.material];
+		uint32_t info = static_cast<uint32_t>(o.material) | ((m.flags & CRT_MAT_TRANSPARENT) ? PRIM_TRANSPARENT : 0u);
+		obj_slot[oi] = static_cast<int32_t>(slot);
+		s->slot_object[slot] = static_cast<int32_t>(oi);
+		if (o.type == CRT_OBJ_SPHERE) {
+			info |= PRIM_SPHERE;
+			prims[3 * slot + 0] = make_float4(o.a[0], o.a[1], o.a[2], o.epsilon);
+			prims[3 * slot + 1] = make_float4(o.b[0], 0.f, 0.f, as_float(info));
+			prims[3 * slot + 2] = make_float4(0.f, 0.f, 0.f, as_float(oi));
+			normals[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+		} else {
+			prims[3 * slot + 0] = make_float4(o.a[0], o.a[1], o.a[2], o.epsilon);
+			prims[3 * slot + 1] = make_float4(o.b[0], o.b[1], o.b[2], as_float(info));
+			prims[3 * slot + 2] = make_float4(o.c[0], o.c[1], o.c[2], as_float(oi));
+			normals[slot] = make_float4(o.n[0], o.n[1], o.n[2], 0.f);
+		}
+	}
+
+	/* ---- upload -------------------------------------------------------------- */
+	std::vector<float4> nodes(4 * bvh.nodes.size());
+	if (!bvh.nodes.empty())
+		std::memcpy(nodes.data(), bvh.nodes.data(), bvh.nodes.size() * sizeof(BvhNode));
+	rc = upload(s, nodes, &s->d.nodes);
+	if (!rc) rc = upload(s, prims, &s->d.prims);
+	if (!rc) rc = upload(s, normals, &s->d.normals);
+	if (!rc) rc = upload(s, planes, &s->d.planes);
+	if (!rc) rc = upload(s, obj_slot, &s->d.obj_slot);
+	if (!rc) rc = upload(s, emitters, &s->d.emitters);
+	if (!rc) rc = upload(s, mats, &s->d.materials);
+	if (!rc && cudaMalloc(&s->tile_counter, sizeof(unsigned int)) != cudaSuccess)
+		rc = fail(CRT_ERR_CUDA, "cudaMalloc(tile counter) failed");
+	if (!rc && cudaMalloc(&s->counters, kNumCounters * sizeof(unsigned long long)) != cudaSuccess)
+		rc = fail(CRT_ERR_CUDA, "cudaMalloc(counters) failed");
+	if (!rc && (cudaEventCreate(&s->ev_start) != cudaSuccess || cudaEventCreate(&s->ev_stop) != cudaSuccess))
+		rc = fail(CRT_ERR_CUDA, "cudaEventCreate failed");
+	if (rc) {
+		crt_scene_destroy(s);
+		return rc;
+	}
+	s->d.num_nodes = static_cast<uint32_t>(bvh.nodes.size());
+	s->d.num_prims = static_cast<uint32_t>(bounded.size());
+	s->d.num_planes = static_cast<uint32_t>(planes.size() / 2);
+	s->d.num_emitters = static_cast<uint32_t>(emitters.size());
+	s->d.num_objects = n;
+	s->d.total_lights = total_lights;
+	std::memcpy(s->d.ambient, desc->ambient, sizeof s->d.ambient);
+
+	s->info.upload_ms = now_ms() - t1;
+	s->info.num_bounded = s->d.num_prims;
+	s->info.num_planes = s->d.num_planes;
+	s->info.num_emitters = s->d.num_emitters;
+	s->info.total_lights = total_lights;
+	s->info.num_nodes = s->d.num_nodes;
+	s->info.max_depth = bvh.max_depth;
+	s->info.device = static_cast<uint32_t>(device);
+	s->info.sm_count = static_cast<uint32_t>(s->sm_count);
+	*out = s;
+	return CRT_OK;
+}
+
+int crt_scene_get_info(const crt_scene *s, crt_scene_info *info)
+{
+	if (!s || !info)
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	*info = s->info;
+	return CRT_OK;
+}
+
+int crt_render_device(crt_scene *s, const crt_render_opts *opts, float *d_raster, float *d_z, void *cuda_stream)
+{
+	if (!s || !opts || !d_raster || !d_z)
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	if (!opts->width || !opts->height)
+		return fail(CRT_ERR_INVALID, "empty image");
+	if (!opts->shard_count || opts->shard_index >= opts->shard_count)
+		return fail(CRT_ERR_INVALID, "bad shard %u of %u", opts->shard_index, opts->shard_count);
+	if (opts->gi_model == CRT_GI_PATH && opts->samples_per_pixel > 0x7fffffffu)
+		return fail(CRT_ERR_INVALID, "too many samples per pixel");
+	CUDA_TRY(cudaSetDevice(s->device));
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	const size_t pixels = static_cast<size_t>(opts->width) * opts->height;
+	const bool count = (opts->flags & CRT_RENDER_COUNT_STATS) != 0;
+
+	/* persistent grid: every resident warp slot of the device */
+	const int per_sm = render_blocks_per_sm(count);
+	if (per_sm <= 0)
+		return fail(CRT_ERR_CUDA, "render kernel cannot be resident (%s)", cudaGetErrorString(cudaGetLastError()));
+	const int grid = per_sm * s->sm_count;
+
+	if (s->row_pos_floats < 3 * pixels) {
+		cudaFree(s->row_pos);
+		s->row_pos = nullptr;
+		s->row_pos_floats = 0;
+		CUDA_TRY(cudaMalloc(&s->row_pos, 3 * pixels * sizeof(float)));
+		s->row_pos_floats = 3 * pixels;
+	}
+	RenderParams p{};
+	p.pending_depth = opts->max_bounces + 4u;
+	const size_t pending_floats = static_cast<size_t>(grid) * kWarpsPerBlock * p.pending_depth * kPendingWords * 32;
+	if (s->pending_floats < pending_floats) {
+		cudaFree(s->pending);
+		s->pending = nullptr;
+		s->pending_floats = 0;
+		CUDA_TRY(cudaMalloc(&s->pending, pending_floats * sizeof(float)));
+		s->pending_floats = pending_floats;
+	}
+
+	p.sc = s->d;
+	p.o = *opts;
+	p.raster = d_raster;
+	p.z_buffer = d_z;
+	p.row_pos = s->row_pos;
+	p.tiles_x = (opts->width + kTileW - 1) / kTileW;
+	p.tiles_y = (opts->height + kTileH - 1) / kTileH;
+	const uint32_t tiles = p.tiles_x * p.tiles_y;
+	const uint32_t chunks = (tiles + kChunkTiles - 1) / kChunkTiles;
+	const uint32_t local_chunks = chunks / opts->shard_count + (opts->shard_index < chunks % opts->shard_count ? 1u : 0u);
+	p.num_local_tiles = local_chunks * kChunkTiles;
+	p.tile_counter = s->tile_counter;
+	p.counters = s->counters;
+	p.pending = s->pending;
+
+	CUDA_TRY(cudaMemsetAsync(s->tile_counter, 0, sizeof(unsigned int), stream));
+	CUDA_TRY(cudaMemsetAsync(s->counters, 0, kNumCounters * sizeof(unsigned long long), stream));
+	/* pixels of other shards (and misses) are zero: the reference relies on fresh zero pages */
+	CUDA_TRY(cudaMemsetAsync(d_raster, 0, 3 * pixels * sizeof(float), stream));
+	CUDA_TRY(cudaMemsetAsync(d_z, 0, pixels * sizeof(float), stream));
+	CUDA_TRY(cudaEventRecord(s->ev_start, stream));
+	launch_raygen_rows(*opts, s->row_pos, stream);
+	launch_render(p, grid, count, stream);
+	CUDA_TRY(cudaEventRecord(s->ev_stop, stream));
+	CUDA_TRY(cudaGetLastError());
+	s->last_stream = stream;
+	s->frame_pending = true;
+	s->frame_counted = count;
+	return CRT_OK;
+}
+
+int crt_render_device_sync(crt_scene *s, crt_stats *stats)
+{
+	if (!s)
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	if (!s->frame_pending)
+		return fail(CRT_ERR_INVALID, "no frame in flight");
+	CUDA_TRY(cudaSetDevice(s->device));
+	CUDA_TRY(cudaEventSynchronize(s->ev_stop));
+	s->frame_pending = false;
+	if (stats) {
+		std::memset(stats, 0, sizeof *stats);
+		float ms = 0.f;
+		CUDA_TRY(cudaEventElapsedTime(&ms, s->ev_start, s->ev_stop));
+		stats->kernel_ms = ms;
+		if (s->frame_counted) {
+			unsigned long long c[kNumCounters];
+			CUDA_TRY(cudaMemcpy(c, s->counters, sizeof c, cudaMemcpyDeviceToHost));
+			stats->rays_closest = c[0];
+			stats->rays_shadow = c[1];
+			stats->box_tests = c[2];
+			stats->tri_tests[0] = c[3];
+			stats->tri_tests[1] = c[4];
+			stats->tri_tests[2] = c[5];
+			stats->tri_tests[3] = c[6];
+			stats->sphere_tests[0] = c[7];
+			stats->sphere_tests[1] = c[8];
+			stats->plane_tests = c[9];
+			stats->nodes_shaded = c[10];
+		}
+	}
+	return CRT_OK;
+}
+
+int crt_render(crt_scene *s, const crt_render_opts *opts, float *raster, float *z_buffer, crt_stats *stats)
+{
+	if (!s || !opts || !raster || !z_buffer)
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	const double t0 = now_ms();
+	CUDA_TRY(cudaSetDevice(s->device));
+	const size_t pixels = static_cast<size_t>(opts->width) * opts->height;
+	if (s->staging_pixels < pixels) {
+		cudaFree(s->d_raster);
+		cudaFree(s->d_z);
+		s->d_raster = s->d_z = nullptr;
+		s->staging_pixels = 0;
+		CUDA_TRY(cudaMalloc(&s->d_raster, 3 * pixels * sizeof(float)));
+		CUDA_TRY(cudaMalloc(&s->d_z, pixels * sizeof(float)));
+		s->staging_pixels = pixels;
+	}
+	int rc = crt_render_device(s, opts, s->d_raster, s->d_z, nullptr);
+	if (rc)
+		return rc;
+	rc = crt_render_device_sync(s, stats);
+	if (rc)
+		return rc;
+	CUDA_TRY(cudaMemcpy(raster, s->d_raster, 3 * pixels * sizeof(float), cudaMemcpyDeviceToHost));
+	CUDA_TRY(cudaMemcpy(z_buffer, s->d_z, pixels * sizeof(float), cudaMemcpyDeviceToHost));
+	if (stats)
+		stats->total_ms = now_ms() - t0;
+	return CRT_OK;
+}
+
+/* ---- ray-batch seams ---------------------------------------------------------- */
+
+namespace {
+struct DeviceBuffer {
+	void *p = nullptr;
+	~DeviceBuffer() { cudaFree(p); }
+	cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 1); }
+};
+} // namespace
+
+int crt_trace_closest(crt_scene *s, const float *rays, size_t n, int32_t *object, float *t, float *normal)
+{
+	if (!s || (n && (!rays || !object || !t)))
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	CUDA_TRY(cudaSetDevice(s->device));
+	DeviceBuffer d_rays, d_obj, d_t, d_n;
+	CUDA_TRY(d_rays.alloc(n * 6 * sizeof(float)));
+	CUDA_TRY(d_obj.alloc(n * sizeof(int32_t)));
+	CUDA_TRY(d_t.alloc(n * sizeof(float)));
+	CUDA_TRY(d_n.alloc(n * 3 * sizeof(float)));
+	CUDA_TRY(cudaMemcpy(d_rays.p, rays, n * 6 * sizeof(float), cudaMemcpyHostToDevice));
+	launch_trace_closest(s->d, static_cast<float *>(d_rays.p), n, static_cast<int32_t *>(d_obj.p), static_cast<float *>(d_t.p),
+		static_cast<float *>(d_n.p), nullptr);
+	CUDA_TRY(cudaGetLastError());
+	CUDA_TRY(cudaMemcpy(object, d_obj.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost));
+	CUDA_TRY(cudaMemcpy(t, d_t.p, n * sizeof(float), cudaMemcpyDeviceToHost));
+	if (normal)
+		CUDA_TRY(cudaMemcpy(normal, d_n.p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+	return CRT_OK;
+}
+
+int crt_trace_shadow(crt_scene *s, const float *rays, const float *dist, const int32_t *emitter, size_t n, float *light, uint8_t *blocked)
+{
+	if (!s || (n && (!rays || !dist || !light || !blocked)))
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	CUDA_TRY(cudaSetDevice(s->device));
+	DeviceBuffer d_rays, d_dist, d_em, d_light, d_blocked;
+	CUDA_TRY(d_rays.alloc(n * 6 * sizeof(float)));
+	CUDA_TRY(d_dist.alloc(n * sizeof(float)));
+	CUDA_TRY(d_em.alloc(n * sizeof(int32_t)));
+	CUDA_TRY(d_light.alloc(n * 3 * sizeof(float)));
+	CUDA_TRY(d_blocked.alloc(n));
+	CUDA_TRY(cudaMemcpy(d_rays.p, rays, n * 6 * sizeof(float), cudaMemcpyHostToDevice));
+	CUDA_TRY(cudaMemcpy(d_dist.p, dist, n * sizeof(float), cudaMemcpyHostToDevice));
+	if (emitter)
+		CUDA_TRY(cudaMemcpy(d_em.p, emitter, n * sizeof(int32_t), cudaMemcpyHostToDevice));
+	CUDA_TRY(cudaMemcpy(d_light.p, light, n * 3 * sizeof(float), cudaMemcpyHostToDevice));
+	launch_trace_shadow(s->d, static_cast<float *>(d_rays.p), static_cast<float *>(d_dist.p),
+		emitter ? static_cast<int32_t *>(d_em.p) : nullptr, n, static_cast<float *>(d_light.p), static_cast<uint8_t *>(d_blocked.p), nullptr);
+	CUDA_TRY(cudaGetLastError());
+	CUDA_TRY(cudaMemcpy(light, d_light.p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+	CUDA_TRY(cudaMemcpy(blocked, d_blocked.p, n, cudaMemcpyDeviceToHost));
+	return CRT_OK;
+}
+
+int crt_texture_eval(crt_scene *s, int32_t material, const float *points, size_t n, float *colors)
+{
+	if (!s || (n && (!points || !colors)))
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	if (material < 0)
+		return fail(CRT_ERR_INVALID, "bad material index %d", material);
+	CUDA_TRY(cudaSetDevice(s->device));
+	DeviceBuffer d_p, d_c;
+	CUDA_TRY(d_p.alloc(n * 3 * sizeof(float)));
+	CUDA_TRY(d_c.alloc(n * 3 * sizeof(float)));
+	CUDA_TRY(cudaMemcpy(d_p.p, points, n * 3 * sizeof(float), cudaMemcpyHostToDevice));
+	launch_texture_eval(s->d, material, static_cast<float *>(d_p.p), n, static_cast<float *>(d_c.p), nullptr);
+	CUDA_TRY(cudaGetLastError());
+	CUDA_TRY(cudaMemcpy(colors, d_c.p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+	return CRT_OK;
+}
+
+int crt_measure_fp32_peak(int device, double *tflops)
+{
+	if (!tflops)
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	int rc = ensure_device(device);
+	if (rc)
+		return rc;
+	int sms = 0;
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+	DeviceBuffer sink;
+	CUDA_TRY(sink.alloc(sizeof(float)));
+	cudaEvent_t a, b;
+	CUDA_TRY(cudaEventCreate(&a));
+	CUDA_TRY(cudaEventCreate(&b));
+	const int blocks = sms * 8, threads = 256, iters = 4096;
+	double best = 0.0;
+	for (int rep = 0; rep < 5; rep++) {
+		CUDA_TRY(cudaEventRecord(a));
+		const double flops = launch_fma_peak(blocks, threads, iters, static_cast<float *>(sink.p), nullptr);
+		CUDA_TRY(cudaEventRecord(b));
+		CUDA_TRY(cudaEventSynchronize(b));
+		float ms = 0.f;
+		CUDA_TRY(cudaEventElapsedTime(&ms, a, b));
+		if (rep > 0 && ms > 0.f)
+			best = std::fmax(best, flops / (ms * 1e-3) / 1e12);
+	}
+	cudaEventDestroy(a);
+	cudaEventDestroy(b);
+	*tflops = best;
+	return CRT_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,47 @@
+/*
+ * crt_kernels.cuh -- launch interface between the C ABI (crt_api.cu) and the
+ * kernels (crt_kernels.cu).
+ */
+#ifndef CRT_KERNELS_CUH
+#define CRT_KERNELS_CUH
+
+#include "crt_device.cuh"
+
+namespace crt {
+
+constexpr int kTileW = 8, kTileH = 4;      /* one warp owns an 8x4 pixel tile: lane = pixel */
+constexpr int kChunkTiles = 8;             /* sharding granularity (crt_render_opts.shard_*) */
+constexpr int kWarpsPerBlock = 8;
+constexpr int kBlockThreads = kWarpsPerBlock * 32;
+constexpr int kNumCounters = 11;
+constexpr int kPendingWords = 13;          /* words per pending-ray record */
+
+struct RenderParams {
+	DScene sc;
+	crt_render_opts o;
+	float *raster;
+	float *z_buffer;
+	const float *row_pos;           /* W*H*3: running-sum pixel positions (raygen_rows_kernel) */
+	uint32_t tiles_x, tiles_y;
+	uint32_t num_local_tiles;       /* tiles of this shard */
+	unsigned int *tile_counter;
+	unsigned long long *counters;   /* kNumCounters, instrumented instance only */
+	float *pending;                 /* per-lane pending-ray stacks */
+	uint32_t pending_depth;
+};
+
+/* grid = number of persistent blocks */
+void launch_raygen_rows(const crt_render_opts &o, float *row_pos, cudaStream_t stream);
+void launch_render(const RenderParams &p, int grid, bool count, cudaStream_t stream);
+int render_blocks_per_sm(bool count);
+
+void launch_trace_closest(const DScene &sc, const float *rays, size_t n, int32_t *object, float *t, float *normal, cudaStream_t stream);
+void launch_trace_shadow(const DScene &sc, const float *rays, const float *dist, const int32_t *emitter, size_t n,
+	float *light, uint8_t *blocked, cudaStream_t stream);
+void launch_texture_eval(const DScene &sc, int32_t material, const float *points, size_t n, float *colors, cudaStream_t stream);
+/* returns FLOPs executed per launch */
+double launch_fma_peak(int blocks, int threads, int iters, float *sink, cudaStream_t stream);
+
+} // namespace crt
+
+#endif

@@ -1,0 +1,134 @@
+"""Binding of the device library csrc/libcrt.so (the C ABI of include/crt.h).
+
+This is the product path: hand-written sm_100a CUDA behind a C ABI.  There is
+no fallback -- if the library is missing or no GPU is usable, calls raise."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _abi
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "csrc", "libcrt.so")
+
+# every symbol include/crt.h declares
+SYMBOLS = [
+    "crt_last_error", "crt_abi_version", "crt_device_count",
+    "crt_scene_create", "crt_scene_destroy", "crt_scene_get_info",
+    "crt_render", "crt_render_device", "crt_render_device_sync",
+    "crt_trace_closest", "crt_trace_shadow", "crt_texture_eval", "crt_measure_fp32_peak",
+]
+
+_lib = None
+
+
+class CrtError(RuntimeError):
+    pass
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise CrtError(f"{LIB_PATH} is missing: build it with `make device` or __graft_entry__.build(); "
+                           "there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        L.crt_last_error.restype = C.c_char_p
+        L.crt_scene_create.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+        L.crt_scene_destroy.argtypes = [C.c_void_p]
+        L.crt_scene_destroy.restype = None
+        L.crt_scene_get_info.argtypes = [C.c_void_p, C.c_void_p]
+        L.crt_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.crt_render_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.crt_render_device_sync.argtypes = [C.c_void_p, C.c_void_p]
+        L.crt_trace_closest.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.crt_trace_shadow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+        L.crt_texture_eval.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.crt_measure_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise CrtError(f"crt error {rc}: {lib().crt_last_error().decode()}")
+
+
+def device_count():
+    return lib().crt_device_count()
+
+
+def measure_fp32_peak(device=0):
+    v = C.c_double()
+    _check(lib().crt_measure_fp32_peak(device, C.byref(v)))
+    return v.value
+
+
+class DeviceScene:
+    """A scene resident on one GPU (crt_scene*).  `scene` is a host.Scene or
+    anything exposing a `desc` (_abi.SceneDesc)."""
+
+    def __init__(self, scene, device=0):
+        self.scene = scene
+        h = C.c_void_p()
+        _check(lib().crt_scene_create(C.addressof(scene.desc), device, C.byref(h)))
+        self._h = h
+        self.info = _abi.SceneInfo()
+        _check(lib().crt_scene_get_info(self._h, C.addressof(self.info)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().crt_scene_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+    def render(self, opts, stats=None):
+        """crt_render: host buffers out (the reference-facing call)."""
+        w, h = opts.width, opts.height
+        raster = np.empty((h, w, 3), dtype=np.float32)
+        z = np.empty((h, w), dtype=np.float32)
+        _check(lib().crt_render(self._h, C.addressof(opts), raster.ctypes.data, z.ctypes.data,
+                                C.addressof(stats) if stats is not None else None))
+        return raster, z
+
+    def render_into(self, opts, raster, z, stats=None):
+        """crt_render into caller-owned host arrays (e.g. pinned memory)."""
+        _check(lib().crt_render(self._h, C.addressof(opts), raster.ctypes.data, z.ctypes.data,
+                                C.addressof(stats) if stats is not None else None))
+
+    def render_device(self, opts, d_raster_ptr, d_z_ptr, stream=None):
+        """crt_render_device: device pointers, enqueued on `stream` (int handle or None)."""
+        _check(lib().crt_render_device(self._h, C.addressof(opts), C.c_void_p(d_raster_ptr), C.c_void_p(d_z_ptr),
+                                       C.c_void_p(stream) if stream else None))
+
+    def sync(self, stats=None):
+        _check(lib().crt_render_device_sync(self._h, C.addressof(stats) if stats is not None else None))
+
+    def trace_closest(self, rays):
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        n = len(rays)
+        obj = np.empty(n, dtype=np.int32)
+        t = np.empty(n, dtype=np.float32)
+        normal = np.zeros((n, 3), dtype=np.float32)
+        _check(lib().crt_trace_closest(self._h, rays.ctypes.data, n, obj.ctypes.data, t.ctypes.data, normal.ctypes.data))
+        return obj, t, normal
+
+    def trace_shadow(self, rays, dist, emitter, light):
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        n = len(rays)
+        dist = np.ascontiguousarray(dist, dtype=np.float32)
+        emitter = np.ascontiguousarray(emitter, dtype=np.int32)
+        light = np.array(light, dtype=np.float32).reshape(n, 3).copy()
+        blocked = np.zeros(n, dtype=np.uint8)
+        _check(lib().crt_trace_shadow(self._h, rays.ctypes.data, dist.ctypes.data, emitter.ctypes.data, n,
+                                      light.ctypes.data, blocked.ctypes.data))
+        return blocked, light
+
+    def texture(self, material, points):
+        pts = np.ascontiguousarray(points, dtype=np.float32).reshape(-1, 3)
+        out = np.zeros_like(pts)
+        _check(lib().crt_texture_eval(self._h, material, pts.ctypes.data, len(pts), out.ctypes.data))
+        return out

@@ -1,0 +1,158 @@
+#!/usr/bin/env python3
+"""Generate the golden fixtures in tests/golden/ by RUNNING THE REFERENCE.
+
+The reference (wojciech-graj/C-Raytracer) ships no tests or known-answer vectors
+(SURVEY section 4), so parity is pinned by executing its unmodified sources,
+compiled in place from /root/reference by oracle/Makefile into
+oracle/_ref/ref_engine (random draws come from the structural stream of
+include/crt_rng.h through -finstrument-functions hooks, oracle/ref_shim.c).
+
+This script only runs where /root/reference exists (the build container).  Its
+outputs are committed so that the CPU suite and the GPU box -- which have no
+reference -- can check the oracle restatement (oracle/crt_oracle.c) and the CUDA
+path against the reference's own results.
+
+    python tests/golden/make_golden.py
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+import _pkg  # noqa: E402
+
+_pkg.load()
+from c_raytracer_b200 import host  # noqa: E402
+from oracle import oracle  # noqa: E402
+
+# (name, scene, width, height, engine flags)
+IMAGE_CASES = [
+    ("scene1_ambient", "scene1", 64, 36, ()),
+    ("scene2_ambient", "scene2", 64, 36, ()),
+    ("scene3_ambient", "scene3", 64, 36, ()),
+    ("scene4_ambient", "scene4", 64, 36, ()),
+    ("scenetest_ambient", "scenetest", 64, 36, ()),
+    ("scenetest2_ambient", "scenetest2", 64, 36, ()),
+    ("scene5s_ambient", "scene5_small", 64, 36, ()),
+    ("scene6s_ambient", "scene6_small", 64, 36, ()),
+    ("scene1_path4", "scene1", 48, 27, ("-g", "path", "-n", "4")),
+    ("scene3_path3", "scene3", 48, 27, ("-g", "path", "-n", "3")),
+    ("scene4_path2", "scene4", 48, 27, ("-g", "path", "-n", "2")),
+    ("scene5s_path4", "scene5_small", 48, 27, ("-g", "path", "-n", "4")),
+    ("scene6s_path4", "scene6_small", 48, 27, ("-g", "path", "-n", "4")),
+    ("scenetest2_path2", "scenetest2", 48, 27, ("-g", "path", "-n", "2")),
+    ("scene1_blinn_lin", "scene1", 48, 27, ("-s", "blinn", "-l", "lin", "-o", "0.5")),
+    ("scene3_none_b3", "scene3", 48, 27, ("-l", "none", "-b", "3", "-a", "0.05")),
+    ("scene3_b0", "scene3", 48, 27, ("-b", "0")),
+    ("scene4_b1_seed7", "scene4", 48, 27, ("-b", "1", "--seed", "7")),
+    ("scenetest_rnorm", "scenetest", 48, 27, ("-r", "norm")),
+    ("scene2_odd_size", "scene2", 37, 23, ()),
+]
+
+RAY_SCENES = ["scene1", "scene3", "scene4", "scenetest", "scenetest2", "scene5_small", "scene6_small"]
+N_RAYS = 1500
+
+
+def seed_of(flags):
+    return int(flags[flags.index("--seed") + 1]) if "--seed" in flags else 1
+
+
+def rescale_of(flags):
+    return flags[flags.index("-r") + 1] if "-r" in flags else None
+
+
+def make_rays(scene, rng, n):
+    """Half camera-like rays, half rays between random points inside the scene's
+    bounded extent; distances and emitters for the shadow query."""
+    objs = scene.objects
+    bounded = objs[objs["type"] != 2]
+    centres = bounded["a"] + np.where((bounded["type"] == 1)[:, None], (bounded["b"] + bounded["c"]) / 3.0, 0.0)
+    lo, hi = centres.min(0) - 1.0, centres.max(0) + 1.0
+    org = rng.uniform(lo, hi, size=(n, 3)).astype(np.float32)
+    tgt = centres[rng.integers(0, len(centres), n)] + rng.normal(0, 0.05, size=(n, 3))
+    d = (tgt - org).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.concatenate([d, org], axis=1).astype(np.float32)
+    dist = rng.uniform(0.2, 12.0, n).astype(np.float32)
+    mats = scene.materials
+    emit_idx = np.nonzero((mats["flags"][objs["material"]] & 4) != 0)[0]
+    emitter = np.where(rng.random(n) < 0.5, emit_idx[rng.integers(0, len(emit_idx), n)], -1).astype(np.int32)
+    light = rng.uniform(0.1, 1.0, size=(n, 3)).astype(np.float32)
+    return rays, dist, emitter, light
+
+
+def main():
+    if not oracle.have_ref():
+        sys.exit("oracle/_ref/ref_engine is missing: run `make -C oracle ref` where /root/reference exists")
+    rng = np.random.default_rng(20240607)
+
+    for name, scene, w, h, flags in IMAGE_CASES:
+        raster, z, cnt = oracle.ref_render(os.path.join("scenes", scene + ".json"), w, h, flags, seed=seed_of(flags))
+        np.savez_compressed(os.path.join(HERE, f"image_{name}.npz"), raster=raster, z=z,
+                            cast_ray=cnt["cast_ray"], shadow=cnt["shadow"], scene=scene, width=w, height=h,
+                            flags=np.array(flags, dtype=str))
+        print(f"image_{name}: {w}x{h} cast_ray {cnt['cast_ray']} shadow {cnt['shadow']} max {raster.max():.4f}")
+
+    for scene in RAY_SCENES:
+        sc = host.Scene(os.path.join(ROOT, "scenes", scene + ".json"))
+        rays, dist, emitter, light = make_rays(sc, rng, N_RAYS)
+        out = oracle.ref_rays(os.path.join("scenes", scene + ".json"), rays, dist, emitter, light)
+        np.savez_compressed(os.path.join(HERE, f"rays_{scene}.npz"), rays=rays, dist=dist, emitter=emitter, light_in=light,
+                            object=out["object"], t=out["t"], normal=out["normal"], blocked=out["blocked"],
+                            light_out=out["light"])
+        print(f"rays_{scene}: hits {(out['object'] >= 0).mean():.2f} blocked {out['blocked'].mean():.2f}")
+
+    # textures: every material of the scenes that use procedural textures, incl. negative coordinates
+    tex = {}
+    for scene in ["scene2", "scene4", "scene5_small", "scene6_small", "scenetest"]:
+        sc = host.Scene(os.path.join(ROOT, "scenes", scene + ".json"))
+        pts = rng.uniform(-6.0, 6.0, size=(800, 3)).astype(np.float32)
+        for mi in range(len(sc.materials)):
+            if sc.materials["tex_type"][mi] == 0 and mi > 0:
+                continue
+            tex[f"{scene}:{mi}:points"] = pts
+            tex[f"{scene}:{mi}:colors"] = oracle.ref_texture(os.path.join("scenes", scene + ".json"), mi, pts)
+    np.savez_compressed(os.path.join(HERE, "textures.npz"), **tex)
+    print("textures:", len(tex) // 2, "materials")
+
+    pts = np.concatenate([rng.uniform(-40, 40, size=(3000, 3)), rng.integers(-5, 6, size=(200, 3)).astype(float),
+                          rng.uniform(-0.01, 0.01, size=(200, 3))]).astype(np.float32)
+    np.savez_compressed(os.path.join(HERE, "noise.npz"), points=pts, values=oracle.ref_noise(pts))
+
+    # primitive known-answer tests through the reference's own moller_trumbore / line_intersects_sphere
+    n = 3000
+    rec = np.zeros((n, 20), dtype=np.float32)
+    kind = rng.integers(0, 2, n)
+    rec[:, 0] = kind
+    rec[:, 1] = np.where(kind == 0, rng.choice([1e-6, 1e-4, 3e-3], n), rng.choice([3e-4, 1e-3], n))
+    v0 = rng.uniform(-2, 2, size=(n, 3))
+    e0 = rng.uniform(-1.5, 1.5, size=(n, 3))
+    e1 = rng.uniform(-1.5, 1.5, size=(n, 3))
+    rec[:, 2:5] = v0
+    rec[:, 5:8] = np.where((kind == 0)[:, None], e0, np.c_[rng.uniform(0.2, 1.5, n), np.zeros(n), np.zeros(n)])
+    rec[:, 8:11] = e1
+    org = rng.uniform(-4, 4, size=(n, 3))
+    # aim at a point of the primitive (or near an edge / tangent) so that about half the cases hit
+    bary = rng.uniform(-0.2, 1.0, size=(n, 2))
+    tgt_tri = v0 + e0 * bary[:, :1] + e1 * bary[:, 1:]
+    dirs = rng.normal(size=(n, 3))
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    tgt_sph = v0 + dirs * rec[:, 5:6] * rng.uniform(0.0, 1.3, size=(n, 1))
+    tgt = np.where((kind == 0)[:, None], tgt_tri, tgt_sph)
+    inside = rng.random(n) < 0.15  # rays starting inside spheres / on the surface
+    org = np.where(((kind == 1) & inside)[:, None], v0 + dirs * rec[:, 5:6] * rng.choice([0.0, 0.5, 1.0], size=(n, 1)), org)
+    d = tgt - org
+    d /= np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-12)
+    rec[:, 14:17] = d
+    rec[:, 17:20] = org
+    out = oracle.ref_kat(rec)
+    np.savez_compressed(os.path.join(HERE, "primitives.npz"), records=rec, hit=out["hit"], t=out["t"])
+    print(f"primitives: hit fraction {out['hit'].mean():.2f}")
+
+
+if __name__ == "__main__":
+    main()
