@@ -106,6 +106,32 @@ def main():
                             light_out=out["light"])
         print(f"rays_{scene}: hits {(out['object'] >= 0).mean():.2f} blocked {out['blocked'].mean():.2f}")
 
+    # scene loader: hashes of the reference's loaded scene (objects in scene order, materials) per file and -r option
+    import hashlib
+    import json
+    import subprocess
+    import tempfile
+    scenes = {}
+    for scene in ["scene1", "scene2", "scene3", "scene4", "scenetest", "scenetest2", "scene5_small", "scene6_small"]:
+        for extra in ((), ("-r", "norm"), ("-r", "0.37")):
+            with tempfile.TemporaryDirectory() as d:
+                out = os.path.join(d, "s.bin")
+                subprocess.run([oracle.REF_ENGINE, "scene", os.path.join("scenes", scene + ".json"), out, *extra],
+                               check=True, cwd=ROOT, stdout=subprocess.DEVNULL)
+                b = open(out, "rb").read()
+            no, nm = np.frombuffer(b[:8], dtype=np.uint32)
+            off = 20 + 14 * 4
+            scenes[scene + ":" + " ".join(extra)] = {
+                "num_objects": int(no), "num_materials": int(nm),
+                "ambient": [float(x) for x in np.frombuffer(b[8:20], dtype=np.float32)],
+                "camera": [float(x) for x in np.frombuffer(b[20:off], dtype=np.float32)],
+                "materials_sha256": hashlib.sha256(b[off:off + 128 * nm]).hexdigest(),
+                "objects_sha256": hashlib.sha256(b[off + 128 * nm:off + 128 * nm + 64 * no]).hexdigest(),
+            }
+    with open(os.path.join(HERE, "scenes.json"), "w") as f:
+        json.dump(scenes, f, indent=1, sort_keys=True)
+    print("scenes:", len(scenes), "loader fixtures")
+
     # textures: every material of the scenes that use procedural textures, incl. negative coordinates
     tex = {}
     for scene in ["scene2", "scene4", "scene5_small", "scene6_small", "scenetest"]:

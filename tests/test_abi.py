@@ -1,0 +1,65 @@
+"""The C ABI: structure layouts agree with the C compiler, libcrt.so loads on a
+machine without a GPU and exports every symbol include/crt.h declares, and the
+product path fails loudly (no CPU fallback) when no device is present."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+from _util import ROOT, scene_path
+from c_raytracer_b200 import _abi, device, host
+
+
+def test_struct_sizes_match_c(tmp_path):
+    src = tmp_path / "sizes.c"
+    src.write_text(
+        '#include <stdio.h>\n#include <stddef.h>\n#include "crt.h"\n'
+        'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(crt_material), sizeof(crt_object),'
+        ' sizeof(crt_scene_desc), sizeof(crt_render_opts), sizeof(crt_stats), sizeof(crt_scene_info),'
+        ' offsetof(crt_render_opts, seed), offsetof(crt_stats, kernel_ms)); return 0;}\n')
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
+    assert got == [C.sizeof(_abi.Material), C.sizeof(_abi.Object), C.sizeof(_abi.SceneDesc), C.sizeof(_abi.RenderOpts),
+                   C.sizeof(_abi.Stats), C.sizeof(_abi.SceneInfo), _abi.RenderOpts.seed.offset, _abi.Stats.kernel_ms.offset]
+    assert got[0] == 128 and got[1] == 64
+
+
+def test_header_symbols_are_exported():
+    if not os.path.exists(device.LIB_PATH):
+        pytest.skip("libcrt.so not built (run __graft_entry__.build())")
+    header = open(os.path.join(ROOT, "include", "crt.h")).read()
+    declared = set(re.findall(r"\b(crt_[a-z0-9_]+)\s*\(", header))
+    assert declared == set(device.SYMBOLS)
+    L = device.lib()
+    for name in declared:
+        assert hasattr(L, name), name
+    assert L.crt_abi_version() == _abi.CRT_ABI_VERSION
+
+
+def test_no_cpu_fallback_without_gpu():
+    if not os.path.exists(device.LIB_PATH):
+        pytest.skip("libcrt.so not built")
+    if device.device_count() > 0:
+        pytest.skip("a GPU is present")
+    sc = host.Scene(scene_path("scene1"))
+    with pytest.raises(device.CrtError, match="no CUDA device"):
+        device.DeviceScene(sc, 0)
+
+
+def test_product_does_not_reference_oracle():
+    """Nothing under the package, src/ or include/ may name the oracle."""
+    bad = []
+    for base in ("c-raytracer_b200", "src", "include", "lib"):
+        for dirpath, _, files in os.walk(os.path.join(ROOT, base)):
+            for f in files:
+                if f.endswith((".so", ".o", ".pyc")):
+                    continue
+                text = open(os.path.join(dirpath, f), errors="ignore").read()
+                if re.search(r"liboracle|oracle_render|from oracle|import oracle|oracle/", text):
+                    bad.append(os.path.join(dirpath, f))
+    # crt_rng.h documents the shared stream and mentions the shim's file name only in a comment
+    bad = [b for b in bad if not b.endswith("crt_rng.h")]
+    assert not bad, bad
