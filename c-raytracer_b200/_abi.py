@@ -16,6 +16,8 @@ CRT_REFLECTION_PHONG, CRT_REFLECTION_BLINN = 0, 1
 CRT_GI_AMBIENT, CRT_GI_PATH = 0, 1
 CRT_ATTEN_NONE, CRT_ATTEN_LINEAR, CRT_ATTEN_SQUARE = 0, 1, 2
 CRT_RENDER_COUNT_STATS = 1
+CRT_FUNC_SIN, CRT_FUNC_SAW, CRT_FUNC_TRIANGLE, CRT_FUNC_SQUARE = 0, 1, 2, 3
+CRT_OK, CRT_ERR_INVALID, CRT_ERR_NO_DEVICE, CRT_ERR_CUDA, CRT_ERR_NOMEM, CRT_ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5
 
 f3 = C.c_float * 3
 
