@@ -41,7 +41,6 @@ enum EntryField {
 
 struct WarpShared {
 	float entry[E_FIELDS][32];
-	float sum[3][32];
 };
 
 /* pending-ray record kinds, stored in the top bits of word 9 */
@@ -82,21 +81,6 @@ __device__ __forceinline__ void pending_load(const float *s, Pending &r)
 	r.inside = __float_as_int(s[10 * 32]);
 	r.node = __float_as_uint(s[11 * 32]);
 	r.aux = __float_as_uint(s[12 * 32]);
-}
-
-/* position of the n-th (0-based) set bit of mask */
-__device__ __forceinline__ uint32_t nth_set_bit(uint32_t mask, uint32_t n)
-{
-	uint32_t pos = 0;
-#pragma unroll
-	for (uint32_t w = 16; w; w >>= 1) {
-		const uint32_t c = (uint32_t)__popc(mask & (((1u << w) - 1u) << pos));
-		if (n >= c) {
-			n -= c;
-			pos += w;
-		}
-	}
-	return pos;
 }
 
 /* eye-segment attenuation applied to every cast_ray result (render.c:292-301) */
@@ -154,6 +138,7 @@ template <bool COUNT>
 __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParams p)
 {
 	__shared__ WarpShared shared[kWarpsPerBlock];
+	__shared__ int wstack[kWarpsPerBlock][kStackSize];
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp_local = threadIdx.x >> 5;
 	const uint32_t warp_global = blockIdx.x * kWarpsPerBlock + warp_local;
@@ -301,104 +286,94 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParam
 					ws.entry[E_SKIP][lane] = __int_as_float(skip);
 				}
 			}
-			ws.sum[0][lane] = 0.f; ws.sum[1][lane] = 0.f; ws.sum[2][lane] = 0.f;
 			const unsigned lit_mask = __ballot_sync(kFull, lit);
 			__syncwarp();
 
-			/* ---- direct light: all (shading point, light sample) pairs of the
-			 * warp, flattened over the lanes (render.c:170-229) ---------------- */
-			const uint32_t total = (uint32_t)__popc(lit_mask) * sc.total_lights;
-			for (uint32_t base = 0; base < total; base += 32u) {
-				const uint32_t f = base + lane;
-				int seg = -1;
-				float cr = 0.f, cg = 0.f, cb = 0.f;
-				uint32_t e_lane = 0;
-				if (f < total) {
-					seg = (int)(f / sc.total_lights);
-					const uint32_t li = f - (uint32_t)seg * sc.total_lights;
-					e_lane = nth_set_bit(lit_mask, (uint32_t)seg);
+			/* ---- direct light (render.c:170-229): the warp takes its lit shading
+			 * points one at a time and traces each point's light samples 32 at a
+			 * time as a packet (packet_shadow): same origin, narrow cone ------- */
+			float sum_r = 0.f, sum_g = 0.f, sum_b = 0.f;
+			for (unsigned todo = lit_mask; todo; todo &= todo - 1u) {
+				const uint32_t e_lane = (uint32_t)__ffs((int)todo) - 1u;
+				const float Px = ws.entry[E_PX][e_lane], Py = ws.entry[E_PY][e_lane], Pz = ws.entry[E_PZ][e_lane];
+				const float Nx = ws.entry[E_NX][e_lane], Ny = ws.entry[E_NY][e_lane], Nz = ws.entry[E_NZ][e_lane];
+				const uint32_t node = __float_as_uint(ws.entry[E_NODE][e_lane]);
+				const int skip_e = __float_as_int(ws.entry[E_SKIP][e_lane]);
+				float pr = 0.f, pg = 0.f, pb = 0.f;
+				for (uint32_t base = 0; base < sc.total_lights; base += 32u) {
+					const uint32_t li = base + lane;
+					bool active = li < sc.total_lights;
 					/* which emitter, which sample */
 					uint32_t ei = 0;
 					while (ei + 1u < sc.num_emitters && li >= sc.emitters[ei + 1u].first_light)
 						ei++;
 					const DEmitter &em = sc.emitters[ei];
-					const int skip_e = __float_as_int(ws.entry[E_SKIP][e_lane]);
-					if ((int)ei != skip_e) {
-						/* draw index counts only the emitters that are sampled, in order */
-						uint32_t l = li;
-						if (skip_e >= 0 && (int)ei > skip_e)
-							l -= sc.emitters[skip_e].num_lights;
-						const float Px = ws.entry[E_PX][e_lane], Py = ws.entry[E_PY][e_lane], Pz = ws.entry[E_PZ][e_lane];
-						const float Nx = ws.entry[E_NX][e_lane], Ny = ws.entry[E_NY][e_lane], Nz = ws.entry[E_NZ][e_lane];
-						const uint32_t node = __float_as_uint(ws.entry[E_NODE][e_lane]);
-						float lx, ly, lz;
-						light_point(em, Px, Py, Pz, node, 2u * l, lx, ly, lz);
-						const float vx = lx - Px, vy = ly - Py, vz = lz - Pz;
-						const float d2 = vx * vx + vy * vy + vz * vz;
-						const float dist = sqrtf(d2);
-						const float inv = 1.f / dist;
-						Ray sr = { Px, Py, Pz, vx * inv, vy * inv, vz * inv };
-						const float a = dot3(sr.dx, sr.dy, sr.dz, Nx, Ny, Nz);
-						float ir = em.ke_n[0], ig = em.ke_n[1], ib = em.ke_n[2];
+					active = active && (int)ei != skip_e;
+					/* draw index counts only the emitters that are sampled, in order */
+					uint32_t l = li;
+					if (skip_e >= 0 && (int)ei > skip_e)
+						l -= sc.emitters[skip_e].num_lights;
+					float lx, ly, lz;
+					light_point(em, Px, Py, Pz, node, 2u * l, lx, ly, lz);
+					const float vx = lx - Px, vy = ly - Py, vz = lz - Pz;
+					const float d2 = vx * vx + vy * vy + vz * vz;
+					const float dist = sqrtf(d2);
+					const float inv = 1.f / dist;
+					const Ray sr = { Px, Py, Pz, vx * inv, vy * inv, vz * inv };
+					float ir = em.ke_n[0], ig = em.ke_n[1], ib = em.ke_n[2];
+					if (active)
 						Cnt<COUNT>::add(cn.shadow);
-						if (!trace_shadow<COUNT>(sc, sr, dist, em.object, ir, ig, ib, cn)) {
-							/* light-segment attenuation (render.c:191-200) */
-							if (o.attenuation == CRT_ATTEN_LINEAR) {
-								const float s = 1.f / (o.attenuation_offset + dist);
-								ir *= s; ig *= s; ib *= s;
-							} else if (o.attenuation == CRT_ATTEN_SQUARE) {
-								const float s = 1.f / (o.attenuation_offset + d2);
-								ir *= s; ig *= s; ib *= s;
-							}
-							const float Dx = ws.entry[E_DX][e_lane], Dy = ws.entry[E_DY][e_lane], Dz = ws.entry[E_DZ][e_lane];
-							float smul;
-							if (o.reflection_model == CRT_REFLECTION_BLINN) {
-								/* H = normalize(D - L), s = -N.H (render.c:215-220) */
-								float bx = Dx - sr.dx, by = Dy - sr.dy, bz = Dz - sr.dz;
-								const float binv = 1.f / sqrtf(bx * bx + by * by + bz * bz);
-								bx *= binv; by *= binv; bz *= binv;
-								smul = -dot3(Nx, Ny, Nz, bx, by, bz);
-							} else {
-								/* R = 2 a N - L, s = -R.D (render.c:210-213) */
-								const float a2 = 2.f * a;
-								smul = -dot3(Nx * a2 - sr.dx, Ny * a2 - sr.dy, Nz * a2 - sr.dz, Dx, Dy, Dz);
-							}
-							/* raw base: negative bases follow powf's rules; fmaxf drops NaN */
-							const float spec = fmaxf(0.f, powf(smul, ws.entry[E_SHIN][e_lane]));
-							const float diff = fmaxf(0.f, a);
-							cr = ws.entry[E_TR][e_lane] * ir * diff + ws.entry[E_KSR][e_lane] * ir * spec;
-							cg = ws.entry[E_TG][e_lane] * ig * diff + ws.entry[E_KSG][e_lane] * ig * spec;
-							cb = ws.entry[E_TB][e_lane] * ib * diff + ws.entry[E_KSB][e_lane] * ib * spec;
+					const bool blocked = packet_shadow<COUNT>(sc, sr, dist, em.object, active, ir, ig, ib, wstack[warp_local], cn);
+					if (active && !blocked) {
+						const float a = dot3(sr.dx, sr.dy, sr.dz, Nx, Ny, Nz);
+						/* light-segment attenuation (render.c:191-200) */
+						if (o.attenuation == CRT_ATTEN_LINEAR) {
+							const float s = 1.f / (o.attenuation_offset + dist);
+							ir *= s; ig *= s; ib *= s;
+						} else if (o.attenuation == CRT_ATTEN_SQUARE) {
+							const float s = 1.f / (o.attenuation_offset + d2);
+							ir *= s; ig *= s; ib *= s;
 						}
+						const float Dx = ws.entry[E_DX][e_lane], Dy = ws.entry[E_DY][e_lane], Dz = ws.entry[E_DZ][e_lane];
+						float smul;
+						if (o.reflection_model == CRT_REFLECTION_BLINN) {
+							/* H = normalize(D - L), s = -N.H (render.c:215-220) */
+							float bx = Dx - sr.dx, by = Dy - sr.dy, bz = Dz - sr.dz;
+							const float binv = 1.f / sqrtf(bx * bx + by * by + bz * bz);
+							bx *= binv; by *= binv; bz *= binv;
+							smul = -dot3(Nx, Ny, Nz, bx, by, bz);
+						} else {
+							/* R = 2 a N - L, s = -R.D (render.c:210-213) */
+							const float a2 = 2.f * a;
+							smul = -dot3(Nx * a2 - sr.dx, Ny * a2 - sr.dy, Nz * a2 - sr.dz, Dx, Dy, Dz);
+						}
+						/* raw base: negative bases follow powf's rules; fmaxf drops NaN */
+						const float spec = fmaxf(0.f, powf(smul, ws.entry[E_SHIN][e_lane]));
+						const float diff = fmaxf(0.f, a);
+						pr += ws.entry[E_TR][e_lane] * ir * diff + ws.entry[E_KSR][e_lane] * ir * spec;
+						pg += ws.entry[E_TG][e_lane] * ig * diff + ws.entry[E_KSG][e_lane] * ig * spec;
+						pb += ws.entry[E_TB][e_lane] * ib * diff + ws.entry[E_KSB][e_lane] * ib * spec;
 					}
 				}
-				__syncwarp();
-				/* fixed-order segmented reduction: lanes of one shading point are contiguous */
+				/* fixed-order butterfly: every lane ends with the same, reproducible sum */
 #pragma unroll
-				for (int off = 1; off < 32; off <<= 1) {
-					const float vr = __shfl_down_sync(kFull, cr, off);
-					const float vg = __shfl_down_sync(kFull, cg, off);
-					const float vb = __shfl_down_sync(kFull, cb, off);
-					const int vs = __shfl_down_sync(kFull, seg, off);
-					if (lane + off < 32u && vs == seg) {
-						cr += vr; cg += vg; cb += vb;
-					}
+				for (int off = 16; off; off >>= 1) {
+					pr += __shfl_xor_sync(kFull, pr, off);
+					pg += __shfl_xor_sync(kFull, pg, off);
+					pb += __shfl_xor_sync(kFull, pb, off);
 				}
-				const int prev = __shfl_up_sync(kFull, seg, 1);
-				if (seg >= 0 && (lane == 0u || prev != seg)) {
-					ws.sum[0][e_lane] += cr;
-					ws.sum[1][e_lane] += cg;
-					ws.sum[2][e_lane] += cb;
+				if (lane == e_lane) {
+					sum_r = pr; sum_g = pg; sum_b = pb;
 				}
-				__syncwarp();
 			}
+			__syncwarp();
 
 			/* ---- accumulate, then spawn children (render.c:239-340) --------- */
 			if (is_hit) {
 				if (lit) {
-					acc_r += ws.sum[0][lane] * wr;
-					acc_g += ws.sum[1][lane] * wg;
-					acc_b += ws.sum[2][lane] * wb;
+					acc_r += sum_r * wr;
+					acc_g += sum_g * wg;
+					acc_b += sum_b * wb;
 				}
 				if (r.remaining > 0u) {
 					const crt_material *m = sc.materials + mat_index;

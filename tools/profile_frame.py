@@ -27,8 +27,13 @@ def main():
     ap.add_argument("height", type=int)
     ap.add_argument("--frames", type=int, default=3)
     ap.add_argument("--count", action="store_true", help="also run one instrumented frame first")
-    ap.add_argument("flags", nargs="*")
-    a = ap.parse_args()
+    argv = sys.argv[1:]
+    flags = []
+    if "--" in argv:
+        k = argv.index("--")
+        argv, flags = argv[:k], argv[k + 1:]
+    a = ap.parse_args(argv)
+    a.flags = flags
     sc = host.Scene(os.path.join(ROOT, "scenes", a.scene + ".json"))
     dev = device.DeviceScene(sc, 0)
     out = {"scene": a.scene, "size": [a.width, a.height], "flags": a.flags,
