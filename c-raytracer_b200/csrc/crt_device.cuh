@@ -243,7 +243,7 @@ struct Hit {
  * the lower scene index wins (the reference's winner depends on its Morton
  * order). */
 template <bool COUNT>
-__device__ __forceinline__ Hit trace_closest(const DScene &sc, const Ray &r, Counters &cn)
+__device__ __forceinline__ Hit trace_closest(const DScene &sc, const Ray &r, int *stack, Counters &cn)
 {
 	Hit best;
 	best.t = FLT_MAX;
@@ -263,7 +263,6 @@ __device__ __forceinline__ Hit trace_closest(const DScene &sc, const Ray &r, Cou
 		return best;
 
 	const RayBox rb = make_raybox(r);
-	int stack[kStackSize];
 	int sp = 0;
 	stack[sp++] = kStackSentinel;
 	int node = 0;
@@ -379,6 +378,74 @@ __device__ __forceinline__ bool trace_shadow(const DScene &sc, const Ray &r, flo
 		}
 	}
 	return false;
+}
+
+/* The two halves of trace_shadow() as a resumable walk, for the render kernel's
+ * refilling lanes: shadow_planes() is the linear plane scan, shadow_walk() runs
+ * one round of the while-while BVH walk (descend to the next leaf, test it) on
+ * the lane's own (node, stack) state.  node == kStackSentinel: walk ended. */
+template <bool COUNT>
+__device__ __forceinline__ bool shadow_planes(const DScene &sc, const Ray &r, float dist, float &lr, float &lg, float &lb, Counters &cn)
+{
+	for (uint32_t k = 0; k < sc.num_planes; k++) {
+		const float4 pl = ldg4(sc.planes + 2 * k);
+		const float4 px = ldg4(sc.planes + 2 * k + 1);
+		float t, a;
+		if (hit_plane<COUNT>(pl, px.x, r, t, a, cn) && t < dist) {
+			const uint32_t info = __float_as_uint(px.y);
+			if (!(info & PRIM_TRANSPARENT))
+				return true;
+			const crt_material *m = sc.materials + (info & PRIM_MATERIAL_MASK);
+			lr *= __ldg(&m->kt[0]);
+			lg *= __ldg(&m->kt[1]);
+			lb *= __ldg(&m->kt[2]);
+		}
+	}
+	return false;
+}
+
+template <bool COUNT>
+__device__ __forceinline__ void shadow_walk(const DScene &sc, const Ray &r, const RayBox &rb, float dist, int emitter_object,
+	int &node, int &sp, int *stack, bool &blocked, float &lr, float &lg, float &lb, Counters &cn)
+{
+	while (node >= 0 && node != kStackSentinel) {
+		const float4 *n = sc.nodes + 4 * node;
+		const float4 xy0 = ldg4(n), xy1 = ldg4(n + 1), z01 = ldg4(n + 2);
+		const float4 ch = ldg4(n + 3);
+		bool h0, h1;
+		float t0, t1;
+		test_children(xy0, xy1, z01, r, rb, dist, h0, h1, t0, t1);
+		Cnt<COUNT>::add(cn.box, 2u);
+		const int c0 = __float_as_int(ch.x), c1 = __float_as_int(ch.y);
+		if (!h0 && !h1) {
+			node = stack[--sp];
+		} else {
+			node = h0 ? c0 : c1;
+			if (h0 && h1)
+				stack[sp++] = c1;
+		}
+	}
+	if (node < 0) {
+		const int leaf = ~node;
+		const int first = leaf >> kLeafBits, count = (leaf & ((1 << kLeafBits) - 1)) + 1;
+		node = stack[--sp];
+		for (int i = 0; i < count; i++) {
+			float t;
+			uint32_t info;
+			int object;
+			if (hit_prim<COUNT>(sc, first + i, r, t, info, object, cn) && t < dist && object != emitter_object) {
+				if (!(info & PRIM_TRANSPARENT)) {
+					blocked = true;
+					node = kStackSentinel;
+					break;
+				}
+				const crt_material *m = sc.materials + (info & PRIM_MATERIAL_MASK);
+				lr *= __ldg(&m->kt[0]);
+				lg *= __ldg(&m->kt[1]);
+				lb *= __ldg(&m->kt[2]);
+			}
+		}
+	}
 }
 
 /* ---- warp-cooperative any-hit ------------------------------------------------

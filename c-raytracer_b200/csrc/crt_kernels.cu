@@ -83,6 +83,21 @@ __device__ __forceinline__ void pending_load(const float *s, Pending &r)
 	r.aux = __float_as_uint(s[12 * 32]);
 }
 
+/* position of the n-th (0-based) set bit of mask */
+__device__ __forceinline__ uint32_t nth_set_bit(uint32_t mask, uint32_t n)
+{
+	uint32_t pos = 0;
+#pragma unroll
+	for (uint32_t w = 16; w; w >>= 1) {
+		const uint32_t c = (uint32_t)__popc(mask & (((1u << w) - 1u) << pos));
+		if (n >= c) {
+			n -= c;
+			pos += w;
+		}
+	}
+	return pos;
+}
+
 /* eye-segment attenuation applied to every cast_ray result (render.c:292-301) */
 __device__ __forceinline__ float eye_attenuation(const crt_render_opts &o, float t)
 {
@@ -137,8 +152,9 @@ __device__ __forceinline__ void flush_counters(const RenderParams &p, Counters &
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParams p)
 {
-	__shared__ WarpShared shared[kWarpsPerBlock];
-	__shared__ int wstack[kWarpsPerBlock][kStackSize];
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	WarpShared *shared = reinterpret_cast<WarpShared *>(smem_raw);
+	float (*wslots)[3][kSlots] = reinterpret_cast<float (*)[3][kSlots]>(smem_raw + sizeof(WarpShared) * kWarpsPerBlock);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp_local = threadIdx.x >> 5;
 	const uint32_t warp_global = blockIdx.x * kWarpsPerBlock + warp_local;
@@ -146,6 +162,7 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParam
 	const DScene &sc = p.sc;
 	const crt_render_opts &o = p.o;
 	Counters cn = {};
+	int stack[kStackSize]; /* the lane's traversal stack (closest-hit walk, then the shadow walks) */
 
 	for (;;) {
 		/* ---- next tile of this shard ------------------------------------- */
@@ -229,7 +246,7 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParam
 					if (r.inside >= 0)
 						found = hit_object<COUNT>(sc, r.inside, ray, hit, cn);
 					if (!found)
-						hit = trace_closest<COUNT>(sc, ray, cn);
+						hit = trace_closest<COUNT>(sc, ray, stack, cn);
 				}
 			}
 			const bool is_hit = have && hit.object >= 0;
@@ -289,84 +306,171 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParam
 			const unsigned lit_mask = __ballot_sync(kFull, lit);
 			__syncwarp();
 
-			/* ---- direct light (render.c:170-229): the warp takes its lit shading
-			 * points one at a time and traces each point's light samples 32 at a
-			 * time as a packet (packet_shadow): same origin, narrow cone ------- */
+			/* ---- direct light (render.c:170-229) --------------------------------
+			 * The (lit shading point x light sample) index space of the warp is cut
+			 * into chunks of <= kSlots shadow rays.  Inside a chunk the lanes pull
+			 * ray indices from a warp counter: a lane whose any-hit walk ends takes
+			 * the next ray as soon as fewer than kRefill lanes are still walking,
+			 * so long walks (through the glass mesh) do not idle the lanes of short
+			 * ones (SIMT efficiency of the walk: 6/32 -> see profiles/).  Every ray
+			 * writes its contribution to its own slot and the slots of a point are
+			 * summed in a fixed order afterwards: the image does not depend on which
+			 * lane traced which ray. ------------------------------------------------ */
 			float sum_r = 0.f, sum_g = 0.f, sum_b = 0.f;
-			for (unsigned todo = lit_mask; todo; todo &= todo - 1u) {
-				const uint32_t e_lane = (uint32_t)__ffs((int)todo) - 1u;
-				const float Px = ws.entry[E_PX][e_lane], Py = ws.entry[E_PY][e_lane], Pz = ws.entry[E_PZ][e_lane];
-				const float Nx = ws.entry[E_NX][e_lane], Ny = ws.entry[E_NY][e_lane], Nz = ws.entry[E_NZ][e_lane];
-				const uint32_t node = __float_as_uint(ws.entry[E_NODE][e_lane]);
-				const int skip_e = __float_as_int(ws.entry[E_SKIP][e_lane]);
-				float pr = 0.f, pg = 0.f, pb = 0.f;
-				for (uint32_t base = 0; base < sc.total_lights; base += 32u) {
-					const uint32_t li = base + lane;
-					bool active = li < sc.total_lights;
-					/* which emitter, which sample */
-					uint32_t ei = 0;
-					while (ei + 1u < sc.num_emitters && li >= sc.emitters[ei + 1u].first_light)
-						ei++;
-					const DEmitter &em = sc.emitters[ei];
-					active = active && (int)ei != skip_e;
-					/* draw index counts only the emitters that are sampled, in order */
-					uint32_t l = li;
-					if (skip_e >= 0 && (int)ei > skip_e)
-						l -= sc.emitters[skip_e].num_lights;
-					float lx, ly, lz;
-					light_point(em, Px, Py, Pz, node, 2u * l, lx, ly, lz);
-					const float vx = lx - Px, vy = ly - Py, vz = lz - Pz;
-					const float d2 = vx * vx + vy * vy + vz * vz;
-					const float dist = sqrtf(d2);
-					const float inv = 1.f / dist;
-					const Ray sr = { Px, Py, Pz, vx * inv, vy * inv, vz * inv };
-					float ir = em.ke_n[0], ig = em.ke_n[1], ib = em.ke_n[2];
-					if (active)
-						Cnt<COUNT>::add(cn.shadow);
-					const bool blocked = packet_shadow<COUNT>(sc, sr, dist, em.object, active, ir, ig, ib, wstack[warp_local], cn);
-					if (active && !blocked) {
-						const float a = dot3(sr.dx, sr.dy, sr.dz, Nx, Ny, Nz);
-						/* light-segment attenuation (render.c:191-200) */
-						if (o.attenuation == CRT_ATTEN_LINEAR) {
-							const float s = 1.f / (o.attenuation_offset + dist);
-							ir *= s; ig *= s; ib *= s;
-						} else if (o.attenuation == CRT_ATTEN_SQUARE) {
-							const float s = 1.f / (o.attenuation_offset + d2);
-							ir *= s; ig *= s; ib *= s;
+			const uint32_t npts = (uint32_t)__popc(lit_mask);
+			const uint32_t L = sc.total_lights;
+			if (npts > 0u && L > 0u) {
+				float *slot_r = wslots[warp_local][0], *slot_g = wslots[warp_local][1], *slot_b = wslots[warp_local][2];
+				const uint32_t pts_per_chunk = (uint32_t)kSlots / L; /* 0: a point spans several chunks */
+				uint32_t p0 = 0, s0 = 0;
+				while (p0 < npts) {
+					uint32_t cpts, cL;
+					if (pts_per_chunk) {
+						cpts = min(pts_per_chunk, npts - p0);
+						cL = L;
+					} else {
+						cpts = 1u;
+						cL = min((uint32_t)kSlots, L - s0);
+					}
+					const uint32_t nwork = cpts * cL;
+					uint32_t next = 0;
+					/* per-lane shadow-ray state */
+					bool have = false;
+					uint32_t w = 0, e_lane = 0;
+					Ray sr = { 0.f, 0.f, 0.f, 0.f, 0.f, 1.f };
+					RayBox rb = {};
+					float dist = 0.f, d2 = 0.f, ir = 0.f, ig = 0.f, ib = 0.f;
+					int em_object = -1, node = kStackSentinel, sp = 0;
+					bool blocked = false;
+					for (;;) {
+						/* -- service: finished lanes shade and store, idle lanes fetch -- */
+						const bool walking = have && node != kStackSentinel;
+						if (have && !walking) {
+							float cr = 0.f, cg = 0.f, cb = 0.f;
+							if (!blocked) {
+								const float Nx = ws.entry[E_NX][e_lane], Ny = ws.entry[E_NY][e_lane], Nz = ws.entry[E_NZ][e_lane];
+								const float a = dot3(sr.dx, sr.dy, sr.dz, Nx, Ny, Nz);
+								/* light-segment attenuation (render.c:191-200) */
+								if (o.attenuation == CRT_ATTEN_LINEAR) {
+									const float s = 1.f / (o.attenuation_offset + dist);
+									ir *= s; ig *= s; ib *= s;
+								} else if (o.attenuation == CRT_ATTEN_SQUARE) {
+									const float s = 1.f / (o.attenuation_offset + d2);
+									ir *= s; ig *= s; ib *= s;
+								}
+								const float Dx = ws.entry[E_DX][e_lane], Dy = ws.entry[E_DY][e_lane], Dz = ws.entry[E_DZ][e_lane];
+								float smul;
+								if (o.reflection_model == CRT_REFLECTION_BLINN) {
+									/* H = normalize(D - L), s = -N.H (render.c:215-220) */
+									float bx = Dx - sr.dx, by = Dy - sr.dy, bz = Dz - sr.dz;
+									const float binv = 1.f / sqrtf(bx * bx + by * by + bz * bz);
+									bx *= binv; by *= binv; bz *= binv;
+									smul = -dot3(Nx, Ny, Nz, bx, by, bz);
+								} else {
+									/* R = 2 a N - L, s = -R.D (render.c:210-213) */
+									const float a2 = 2.f * a;
+									smul = -dot3(Nx * a2 - sr.dx, Ny * a2 - sr.dy, Nz * a2 - sr.dz, Dx, Dy, Dz);
+								}
+								/* raw base: negative bases follow powf's rules; fmaxf drops NaN */
+								const float spec = fmaxf(0.f, powf(smul, ws.entry[E_SHIN][e_lane]));
+								const float diff = fmaxf(0.f, a);
+								cr = ws.entry[E_TR][e_lane] * ir * diff + ws.entry[E_KSR][e_lane] * ir * spec;
+								cg = ws.entry[E_TG][e_lane] * ig * diff + ws.entry[E_KSG][e_lane] * ig * spec;
+								cb = ws.entry[E_TB][e_lane] * ib * diff + ws.entry[E_KSB][e_lane] * ib * spec;
+							}
+							slot_r[w] = cr; slot_g[w] = cg; slot_b[w] = cb;
+							have = false;
 						}
-						const float Dx = ws.entry[E_DX][e_lane], Dy = ws.entry[E_DY][e_lane], Dz = ws.entry[E_DZ][e_lane];
-						float smul;
-						if (o.reflection_model == CRT_REFLECTION_BLINN) {
-							/* H = normalize(D - L), s = -N.H (render.c:215-220) */
-							float bx = Dx - sr.dx, by = Dy - sr.dy, bz = Dz - sr.dz;
-							const float binv = 1.f / sqrtf(bx * bx + by * by + bz * bz);
-							bx *= binv; by *= binv; bz *= binv;
-							smul = -dot3(Nx, Ny, Nz, bx, by, bz);
-						} else {
-							/* R = 2 a N - L, s = -R.D (render.c:210-213) */
-							const float a2 = 2.f * a;
-							smul = -dot3(Nx * a2 - sr.dx, Ny * a2 - sr.dy, Nz * a2 - sr.dz, Dx, Dy, Dz);
+						/* lanes still walking keep their ray; the others take the next indices */
+						const unsigned free_mask = __ballot_sync(kFull, !walking);
+						if (!walking) {
+							w = next + (uint32_t)__popc(free_mask & ((1u << lane) - 1u));
+							if (w < nwork) {
+								have = true;
+								blocked = false;
+								node = kStackSentinel;
+								const uint32_t q = w / cL;
+								const uint32_t li = s0 + (w - q * cL);
+								e_lane = nth_set_bit(lit_mask, p0 + q);
+								/* which emitter, which sample */
+								uint32_t ei = 0;
+								while (ei + 1u < sc.num_emitters && li >= sc.emitters[ei + 1u].first_light)
+									ei++;
+								const DEmitter &em = sc.emitters[ei];
+								const int skip_e = __float_as_int(ws.entry[E_SKIP][e_lane]);
+								if ((int)ei == skip_e) {
+									blocked = true; /* the hit object is not its own light (render.c:172): no ray */
+								} else {
+									/* draw index counts only the emitters that are sampled, in order */
+									uint32_t l = li;
+									if (skip_e >= 0 && (int)ei > skip_e)
+										l -= sc.emitters[skip_e].num_lights;
+									const float Px = ws.entry[E_PX][e_lane], Py = ws.entry[E_PY][e_lane], Pz = ws.entry[E_PZ][e_lane];
+									float lx, ly, lz;
+									light_point(em, Px, Py, Pz, __float_as_uint(ws.entry[E_NODE][e_lane]), 2u * l, lx, ly, lz);
+									const float vx = lx - Px, vy = ly - Py, vz = lz - Pz;
+									d2 = vx * vx + vy * vy + vz * vz;
+									dist = sqrtf(d2);
+									const float inv = 1.f / dist;
+									sr.ox = Px; sr.oy = Py; sr.oz = Pz;
+									sr.dx = vx * inv; sr.dy = vy * inv; sr.dz = vz * inv;
+									ir = em.ke_n[0]; ig = em.ke_n[1]; ib = em.ke_n[2];
+									em_object = em.object;
+									Cnt<COUNT>::add(cn.shadow);
+									blocked = shadow_planes<COUNT>(sc, sr, dist, ir, ig, ib, cn);
+									if (!blocked && sc.num_nodes != 0u) {
+										rb = make_raybox(sr);
+										stack[0] = kStackSentinel;
+										sp = 1;
+										node = 0;
+									}
+								}
+							}
 						}
-						/* raw base: negative bases follow powf's rules; fmaxf drops NaN */
-						const float spec = fmaxf(0.f, powf(smul, ws.entry[E_SHIN][e_lane]));
-						const float diff = fmaxf(0.f, a);
-						pr += ws.entry[E_TR][e_lane] * ir * diff + ws.entry[E_KSR][e_lane] * ir * spec;
-						pg += ws.entry[E_TG][e_lane] * ig * diff + ws.entry[E_KSG][e_lane] * ig * spec;
-						pb += ws.entry[E_TB][e_lane] * ib * diff + ws.entry[E_KSB][e_lane] * ib * spec;
+						next += (uint32_t)__popc(free_mask);
+						if (!__any_sync(kFull, have))
+							break;
+						/* -- walk until fewer than `keep` lanes are still walking -------- */
+						const uint32_t keep = next < nwork ? (uint32_t)kRefill : 1u;
+						for (;;) {
+							if (have)
+								shadow_walk<COUNT>(sc, sr, rb, dist, em_object, node, sp, stack, blocked, ir, ig, ib, cn);
+							if ((uint32_t)__popc(__ballot_sync(kFull, have && node != kStackSentinel)) < keep)
+								break;
+						}
+						/* lanes whose walk ended are retired at the top of the loop */
+					}
+					__syncwarp();
+					/* fixed-order sums of the chunk's points */
+					for (uint32_t q = 0; q < cpts; q++) {
+						float a = 0.f, b = 0.f, c = 0.f;
+						for (uint32_t i = lane; i < cL; i += 32u) {
+							a += slot_r[q * cL + i];
+							b += slot_g[q * cL + i];
+							c += slot_b[q * cL + i];
+						}
+#pragma unroll
+						for (int off = 16; off; off >>= 1) {
+							a += __shfl_xor_sync(kFull, a, off);
+							b += __shfl_xor_sync(kFull, b, off);
+							c += __shfl_xor_sync(kFull, c, off);
+						}
+						if (lane == nth_set_bit(lit_mask, p0 + q)) {
+							sum_r += a; sum_g += b; sum_b += c;
+						}
+					}
+					__syncwarp();
+					if (pts_per_chunk) {
+						p0 += cpts;
+					} else {
+						s0 += cL;
+						if (s0 >= L) {
+							s0 = 0;
+							p0++;
+						}
 					}
 				}
-				/* fixed-order butterfly: every lane ends with the same, reproducible sum */
-#pragma unroll
-				for (int off = 16; off; off >>= 1) {
-					pr += __shfl_xor_sync(kFull, pr, off);
-					pg += __shfl_xor_sync(kFull, pg, off);
-					pb += __shfl_xor_sync(kFull, pb, off);
-				}
-				if (lane == e_lane) {
-					sum_r = pr; sum_g = pg; sum_b = pb;
-				}
 			}
-			__syncwarp();
 
 			/* ---- accumulate, then spawn children (render.c:239-340) --------- */
 			if (is_hit) {
@@ -495,7 +599,8 @@ __global__ void trace_closest_kernel(DScene sc, const float *rays, size_t n, int
 		return;
 	Counters cn = {};
 	const Ray r = { rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5], rays[6 * i], rays[6 * i + 1], rays[6 * i + 2] };
-	const Hit h = trace_closest<false>(sc, r, cn);
+	int stack[kStackSize];
+	const Hit h = trace_closest<false>(sc, r, stack, cn);
 	object[i] = h.object;
 	t[i] = h.t;
 	if (normal) {
@@ -563,22 +668,27 @@ void launch_raygen_rows(const crt_render_opts &o, float *row_pos, cudaStream_t s
 	raygen_rows_kernel<<<(o.height + threads - 1) / threads, threads, 0, stream>>>(o, row_pos);
 }
 
+constexpr size_t kRenderSmem = (sizeof(WarpShared) + sizeof(float) * 3 * kSlots) * kWarpsPerBlock;
+
 int render_blocks_per_sm(bool count)
 {
 	int n = 0;
-	if (count)
-		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_kernel<true>, kBlockThreads, 0);
-	else
-		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_kernel<false>, kBlockThreads, 0);
+	if (count) {
+		cudaFuncSetAttribute(render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRenderSmem);
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_kernel<true>, kBlockThreads, kRenderSmem);
+	} else {
+		cudaFuncSetAttribute(render_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRenderSmem);
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_kernel<false>, kBlockThreads, kRenderSmem);
+	}
 	return n;
 }
 
 void launch_render(const RenderParams &p, int grid, bool count, cudaStream_t stream)
 {
 	if (count)
-		render_kernel<true><<<grid, kBlockThreads, 0, stream>>>(p);
+		render_kernel<true><<<grid, kBlockThreads, kRenderSmem, stream>>>(p);
 	else
-		render_kernel<false><<<grid, kBlockThreads, 0, stream>>>(p);
+		render_kernel<false><<<grid, kBlockThreads, kRenderSmem, stream>>>(p);
 }
 
 void launch_trace_closest(const DScene &sc, const float *rays, size_t n, int32_t *object, float *t, float *normal, cudaStream_t stream)

@@ -15,6 +15,8 @@ constexpr int kWarpsPerBlock = 8;
 constexpr int kBlockThreads = kWarpsPerBlock * 32;
 constexpr int kNumCounters = 11;
 constexpr int kPendingWords = 13;          /* words per pending-ray record */
+constexpr int kSlots = 640;                /* shadow-ray contribution slots per warp (one chunk) */
+constexpr int kRefill = 20;                /* lanes fetch new shadow rays when fewer than this many are walking */
 
 struct RenderParams {
 	DScene sc;
