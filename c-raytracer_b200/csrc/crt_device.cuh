@@ -380,10 +380,8 @@ __device__ __forceinline__ bool trace_shadow(const DScene &sc, const Ray &r, flo
 	return false;
 }
 
-/* The two halves of trace_shadow() as a resumable walk, for the render kernel's
- * refilling lanes: shadow_planes() is the linear plane scan, shadow_walk() runs
- * one round of the while-while BVH walk (descend to the next leaf, test it) on
- * the lane's own (node, stack) state.  node == kStackSentinel: walk ended. */
+/* trace_shadow() in resumable pieces for the render kernel's refilling lanes:
+ * shadow_planes() is the linear plane scan, the ShadowWalk steps below walk the BVH. */
 template <bool COUNT>
 __device__ __forceinline__ bool shadow_planes(const DScene &sc, const Ray &r, float dist, float &lr, float &lg, float &lb, Counters &cn)
 {
@@ -404,47 +402,112 @@ __device__ __forceinline__ bool shadow_planes(const DScene &sc, const Ray &r, fl
 	return false;
 }
 
-template <bool COUNT>
-__device__ __forceinline__ void shadow_walk(const DScene &sc, const Ray &r, const RayBox &rb, float dist, int emitter_object,
-	int &node, int &sp, int *stack, bool &blocked, float &lr, float &lg, float &lb, Counters &cn)
+/* Any-hit order is free (every occluder within dist counts, accel.c:360-387),
+ * so the walk is split into two kinds of unit steps that a lane can take in
+ * any interleaving: an INNER step (one node: two slab tests, hit leaves go to
+ * the lane's leaf queue, hit inner children to its stack) and a PRIM step (one
+ * primitive of the queued leaves).  The render kernel lets the warp vote each
+ * iteration for the kind more lanes are ready for, instead of a while-while
+ * loop in which lanes at a leaf wait for the longest descent of the warp. */
+constexpr int kLeafQueue = 8; /* queued leaf codes per lane (shared memory, [slot][lane]) */
+
+struct ShadowWalk {
+	int node;       /* next inner node, kStackSentinel: none */
+	int sp;         /* stack[0] = kStackSentinel */
+	int leaf_first; /* primitive slot being tested next */
+	int leaf_left;  /* primitives left in the current leaf */
+	int qhead, qcount;
+};
+
+__device__ __forceinline__ void shadow_walk_reset(ShadowWalk &w)
 {
-	while (node >= 0 && node != kStackSentinel) {
-		const float4 *n = sc.nodes + 4 * node;
-		const float4 xy0 = ldg4(n), xy1 = ldg4(n + 1), z01 = ldg4(n + 2);
-		const float4 ch = ldg4(n + 3);
-		bool h0, h1;
-		float t0, t1;
-		test_children(xy0, xy1, z01, r, rb, dist, h0, h1, t0, t1);
-		Cnt<COUNT>::add(cn.box, 2u);
-		const int c0 = __float_as_int(ch.x), c1 = __float_as_int(ch.y);
-		if (!h0 && !h1) {
-			node = stack[--sp];
+	w.node = kStackSentinel;
+	w.sp = 0;
+	w.leaf_first = 0;
+	w.leaf_left = 0;
+	w.qhead = 0;
+	w.qcount = 0;
+}
+
+__device__ __forceinline__ bool shadow_walk_busy(const ShadowWalk &w)
+{
+	return w.node != kStackSentinel || w.leaf_left > 0 || w.qcount > 0;
+}
+
+__device__ __forceinline__ bool shadow_can_inner(const ShadowWalk &w)
+{
+	return w.node != kStackSentinel && w.qcount <= kLeafQueue - 2;
+}
+
+__device__ __forceinline__ bool shadow_can_prim(const ShadowWalk &w)
+{
+	return w.leaf_left > 0 || w.qcount > 0;
+}
+
+/* queue: this lane's column of q[kLeafQueue][32] */
+template <bool COUNT>
+__device__ __forceinline__ void shadow_inner_step(const DScene &sc, const Ray &r, const RayBox &rb, float dist, ShadowWalk &w,
+	int *stack, int *q, Counters &cn)
+{
+	const float4 *n = sc.nodes + 4 * w.node;
+	const float4 xy0 = ldg4(n), xy1 = ldg4(n + 1), z01 = ldg4(n + 2);
+	const float4 ch = ldg4(n + 3);
+	bool h0, h1;
+	float t0, t1;
+	test_children(xy0, xy1, z01, r, rb, dist, h0, h1, t0, t1);
+	Cnt<COUNT>::add(cn.box, 2u);
+	const int c0 = __float_as_int(ch.x), c1 = __float_as_int(ch.y);
+	int next = kStackSentinel;
+	if (h0) {
+		if (c0 < 0) {
+			q[((w.qhead + w.qcount) & (kLeafQueue - 1)) * 32] = c0;
+			w.qcount++;
 		} else {
-			node = h0 ? c0 : c1;
-			if (h0 && h1)
-				stack[sp++] = c1;
+			next = c0;
 		}
 	}
-	if (node < 0) {
-		const int leaf = ~node;
-		const int first = leaf >> kLeafBits, count = (leaf & ((1 << kLeafBits) - 1)) + 1;
-		node = stack[--sp];
-		for (int i = 0; i < count; i++) {
-			float t;
-			uint32_t info;
-			int object;
-			if (hit_prim<COUNT>(sc, first + i, r, t, info, object, cn) && t < dist && object != emitter_object) {
-				if (!(info & PRIM_TRANSPARENT)) {
-					blocked = true;
-					node = kStackSentinel;
-					break;
-				}
-				const crt_material *m = sc.materials + (info & PRIM_MATERIAL_MASK);
-				lr *= __ldg(&m->kt[0]);
-				lg *= __ldg(&m->kt[1]);
-				lb *= __ldg(&m->kt[2]);
-			}
+	if (h1) {
+		if (c1 < 0) {
+			q[((w.qhead + w.qcount) & (kLeafQueue - 1)) * 32] = c1;
+			w.qcount++;
+		} else if (next == kStackSentinel) {
+			next = c1;
+		} else {
+			stack[w.sp++] = c1;
 		}
+	}
+	if (next == kStackSentinel)
+		next = stack[--w.sp]; /* stack[0] is the sentinel */
+	w.node = next;
+}
+
+template <bool COUNT>
+__device__ __forceinline__ void shadow_prim_step(const DScene &sc, const Ray &r, float dist, int emitter_object, ShadowWalk &w,
+	int *q, bool &blocked, float &lr, float &lg, float &lb, Counters &cn)
+{
+	if (w.leaf_left == 0) {
+		const int leaf = ~q[w.qhead * 32];
+		w.qhead = (w.qhead + 1) & (kLeafQueue - 1);
+		w.qcount--;
+		w.leaf_first = leaf >> kLeafBits;
+		w.leaf_left = (leaf & ((1 << kLeafBits) - 1)) + 1;
+	}
+	float t;
+	uint32_t info;
+	int object;
+	const bool hit = hit_prim<COUNT>(sc, w.leaf_first, r, t, info, object, cn);
+	w.leaf_first++;
+	w.leaf_left--;
+	if (hit && t < dist && object != emitter_object) {
+		if (!(info & PRIM_TRANSPARENT)) {
+			blocked = true;
+			shadow_walk_reset(w); /* first opaque occluder ends the walk (accel.c:369-371) */
+			return;
+		}
+		const crt_material *m = sc.materials + (info & PRIM_MATERIAL_MASK);
+		lr *= __ldg(&m->kt[0]);
+		lg *= __ldg(&m->kt[1]);
+		lb *= __ldg(&m->kt[2]);
 	}
 }
 

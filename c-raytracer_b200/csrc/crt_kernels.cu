@@ -155,6 +155,7 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParam
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	WarpShared *shared = reinterpret_cast<WarpShared *>(smem_raw);
 	float (*wslots)[3][kSlots] = reinterpret_cast<float (*)[3][kSlots]>(smem_raw + sizeof(WarpShared) * kWarpsPerBlock);
+	int *wqueue = reinterpret_cast<int *>(smem_raw + (sizeof(WarpShared) + sizeof(float) * 3 * kSlots) * kWarpsPerBlock);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp_local = threadIdx.x >> 5;
 	const uint32_t warp_global = blockIdx.x * kWarpsPerBlock + warp_local;
@@ -340,11 +341,14 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParam
 					Ray sr = { 0.f, 0.f, 0.f, 0.f, 0.f, 1.f };
 					RayBox rb = {};
 					float dist = 0.f, d2 = 0.f, ir = 0.f, ig = 0.f, ib = 0.f;
-					int em_object = -1, node = kStackSentinel, sp = 0;
+					int em_object = -1;
 					bool blocked = false;
+					ShadowWalk sw;
+					shadow_walk_reset(sw);
+					int *q = wqueue + warp_local * (kLeafQueue * 32) + lane;
 					for (;;) {
 						/* -- service: finished lanes shade and store, idle lanes fetch -- */
-						const bool walking = have && node != kStackSentinel;
+						const bool walking = have && shadow_walk_busy(sw);
 						if (have && !walking) {
 							float cr = 0.f, cg = 0.f, cb = 0.f;
 							if (!blocked) {
@@ -388,7 +392,7 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParam
 							if (w < nwork) {
 								have = true;
 								blocked = false;
-								node = kStackSentinel;
+								shadow_walk_reset(sw);
 								const uint32_t q = w / cL;
 								const uint32_t li = s0 + (w - q * cL);
 								e_lane = nth_set_bit(lit_mask, p0 + q);
@@ -421,8 +425,8 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParam
 									if (!blocked && sc.num_nodes != 0u) {
 										rb = make_raybox(sr);
 										stack[0] = kStackSentinel;
-										sp = 1;
-										node = 0;
+										sw.sp = 1;
+										sw.node = 0;
 									}
 								}
 							}
@@ -430,12 +434,21 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParam
 						next += (uint32_t)__popc(free_mask);
 						if (!__any_sync(kFull, have))
 							break;
-						/* -- walk until fewer than `keep` lanes are still walking -------- */
+						/* -- walk until fewer than `keep` lanes are still walking: each
+						 * iteration the warp takes the kind of step more lanes are ready for */
 						const uint32_t keep = next < nwork ? (uint32_t)kRefill : 1u;
 						for (;;) {
-							if (have)
-								shadow_walk<COUNT>(sc, sr, rb, dist, em_object, node, sp, stack, blocked, ir, ig, ib, cn);
-							if ((uint32_t)__popc(__ballot_sync(kFull, have && node != kStackSentinel)) < keep)
+							const bool ci = have && shadow_can_inner(sw), cp = have && shadow_can_prim(sw);
+							const uint32_t ni = (uint32_t)__popc(__ballot_sync(kFull, ci));
+							const uint32_t np = (uint32_t)__popc(__ballot_sync(kFull, cp));
+							if (ni >= np) {
+								if (ci)
+									shadow_inner_step<COUNT>(sc, sr, rb, dist, sw, stack, q, cn);
+							} else {
+								if (cp)
+									shadow_prim_step<COUNT>(sc, sr, dist, em_object, sw, q, blocked, ir, ig, ib, cn);
+							}
+							if ((uint32_t)__popc(__ballot_sync(kFull, have && shadow_walk_busy(sw))) < keep)
 								break;
 						}
 						/* lanes whose walk ended are retired at the top of the loop */
@@ -668,7 +681,7 @@ void launch_raygen_rows(const crt_render_opts &o, float *row_pos, cudaStream_t s
 	raygen_rows_kernel<<<(o.height + threads - 1) / threads, threads, 0, stream>>>(o, row_pos);
 }
 
-constexpr size_t kRenderSmem = (sizeof(WarpShared) + sizeof(float) * 3 * kSlots) * kWarpsPerBlock;
+constexpr size_t kRenderSmem = (sizeof(WarpShared) + sizeof(float) * 3 * kSlots + sizeof(int) * kLeafQueue * 32) * kWarpsPerBlock;
 
 int render_blocks_per_sm(bool count)
 {
