@@ -212,10 +212,12 @@ void build_bvh(const std::vector<Aabb> &boxes, BvhResult &out)
 		/* the whole scene fits one leaf: wrap it so that node 0 is an inner node */
 		BvhNode node;
 		std::memset(&node, 0, sizeof node);
+		/* a far-away point box: the slab test misses it for every ray (an inverted
+		 * box would pass a min/max slab test) */
 		Aabb empty;
 		for (int k = 0; k < 3; k++) {
-			empty.lo[k] = FLT_MAX;
-			empty.hi[k] = -FLT_MAX;
+			empty.lo[k] = 1e30f;
+			empty.hi[k] = 1e30f;
 		}
 		store_child(node, 0, root, root_box);
 		store_child(node, 1, encode_leaf(0, 1), empty);

@@ -373,7 +373,8 @@ int crt_render_device(crt_scene *s, const crt_render_opts *opts, float *d_raster
 	}
 	RenderParams p{};
 	p.pending_depth = opts->max_bounces + 4u;
-	const size_t pending_floats = static_cast<size_t>(grid) * kWarpsPerBlock * p.pending_depth * kPendingWords * 32;
+	const size_t slots_floats = static_cast<size_t>(grid) * kWarpsPerBlock * 3 * kSlots;
+	const size_t pending_floats = static_cast<size_t>(grid) * kWarpsPerBlock * p.pending_depth * kPendingWords * 32 + slots_floats;
 	if (s->pending_floats < pending_floats) {
 		cudaFree(s->pending);
 		s->pending = nullptr;
@@ -396,6 +397,7 @@ int crt_render_device(crt_scene *s, const crt_render_opts *opts, float *d_raster
 	p.tile_counter = s->tile_counter;
 	p.counters = s->counters;
 	p.pending = s->pending;
+	p.slots = s->pending + (pending_floats - slots_floats);
 
 	CUDA_TRY(cudaMemsetAsync(s->tile_counter, 0, sizeof(unsigned int), stream));
 	CUDA_TRY(cudaMemsetAsync(s->counters, 0, kNumCounters * sizeof(unsigned long long), stream));

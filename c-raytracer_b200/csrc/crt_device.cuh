@@ -511,120 +511,6 @@ __device__ __forceinline__ void shadow_prim_step(const DScene &sc, const Ray &r,
 	}
 }
 
-/* ---- warp-cooperative any-hit ------------------------------------------------
- * The 32 lanes of a warp trace 32 shadow rays of ONE shading point (same
- * origin, directions inside the narrow cone towards one small light) as a
- * packet: one traversal stack per warp in shared memory, a node is visited
- * iff the ballot of the live lanes hits its box, every node / primitive
- * fetch is one warp-uniform load, and all control flow is warp-uniform.
- * Each lane still performs its own exact primitive tests, so the per-ray
- * result (blocked, product of kt) is that of trace_shadow() above.
- *
- * Leaves are processed while their parent is visited, predicated on the
- * lane's own box test, so only inner nodes are ever pushed. */
-
-template <bool COUNT>
-__device__ __forceinline__ void packet_leaf(const DScene &sc, int leafcode, const Ray &r, float dist, int emitter_object,
-	bool lane_in, bool &alive, bool &blocked, float &lr, float &lg, float &lb, Counters &cn)
-{
-	const int leaf = ~leafcode;
-	const int first = leaf >> kLeafBits, count = (leaf & ((1 << kLeafBits) - 1)) + 1;
-	for (int i = 0; i < count; i++) {
-		const float4 p0 = ldg4(sc.prims + 3 * (first + i));
-		const float4 p1 = ldg4(sc.prims + 3 * (first + i) + 1);
-		const float4 p2 = ldg4(sc.prims + 3 * (first + i) + 2);
-		if (lane_in && alive) {
-			const uint32_t info = __float_as_uint(p1.w);
-			float t;
-			const bool hit = (info & PRIM_SPHERE) ? hit_sphere<COUNT>(p0, p1.x, r, t, cn) : hit_triangle<COUNT>(p0, p1, p2, r, t, cn);
-			if (hit && t < dist && __float_as_int(p2.w) != emitter_object) {
-				if (!(info & PRIM_TRANSPARENT)) {
-					alive = false;
-					blocked = true;
-				} else {
-					const crt_material *m = sc.materials + (info & PRIM_MATERIAL_MASK);
-					lr *= __ldg(&m->kt[0]);
-					lg *= __ldg(&m->kt[1]);
-					lb *= __ldg(&m->kt[2]);
-				}
-			}
-		}
-	}
-}
-
-/* `active` lanes carry a ray; returns true for a lane whose ray is blocked.
- * `wstack` is this warp's kStackSize ints of shared memory. */
-template <bool COUNT>
-__device__ __forceinline__ bool packet_shadow(const DScene &sc, const Ray &r, float dist, int emitter_object, bool active,
-	float &lr, float &lg, float &lb, int *wstack, Counters &cn)
-{
-	constexpr unsigned kAll = 0xffffffffu;
-	bool alive = active, blocked = false;
-	for (uint32_t k = 0; k < sc.num_planes; k++) {
-		const float4 pl = ldg4(sc.planes + 2 * k);
-		const float4 px = ldg4(sc.planes + 2 * k + 1);
-		if (alive) {
-			float t, a;
-			if (hit_plane<COUNT>(pl, px.x, r, t, a, cn) && t < dist) {
-				const uint32_t info = __float_as_uint(px.y);
-				if (!(info & PRIM_TRANSPARENT)) {
-					alive = false;
-					blocked = true;
-				} else {
-					const crt_material *m = sc.materials + (info & PRIM_MATERIAL_MASK);
-					lr *= __ldg(&m->kt[0]);
-					lg *= __ldg(&m->kt[1]);
-					lb *= __ldg(&m->kt[2]);
-				}
-			}
-		}
-	}
-	if (sc.num_nodes == 0 || !__any_sync(kAll, alive))
-		return blocked;
-
-	const RayBox rb = make_raybox(r);
-	int sp = 0;
-	int node = 0;
-	for (;;) {
-		const float4 *n = sc.nodes + 4 * node;
-		const float4 xy0 = ldg4(n), xy1 = ldg4(n + 1), z01 = ldg4(n + 2);
-		const float4 ch = ldg4(n + 3);
-		bool h0, h1;
-		float t0, t1;
-		test_children(xy0, xy1, z01, r, rb, dist, h0, h1, t0, t1);
-		if (alive)
-			Cnt<COUNT>::add(cn.box, 2u);
-		h0 = h0 && alive;
-		h1 = h1 && alive;
-		const int c0 = __float_as_int(ch.x), c1 = __float_as_int(ch.y);
-		const bool any0 = __any_sync(kAll, h0), any1 = __any_sync(kAll, h1);
-		int next = kStackSentinel;
-		if (any0) {
-			if (c0 < 0)
-				packet_leaf<COUNT>(sc, c0, r, dist, emitter_object, h0, alive, blocked, lr, lg, lb, cn);
-			else
-				next = c0;
-		}
-		if (any1) {
-			if (c1 < 0)
-				packet_leaf<COUNT>(sc, c1, r, dist, emitter_object, h1, alive, blocked, lr, lg, lb, cn);
-			else if (next == kStackSentinel)
-				next = c1;
-			else
-				wstack[sp++] = c1;
-		}
-		if (!__any_sync(kAll, alive))
-			break;
-		if (next == kStackSentinel) {
-			if (sp == 0)
-				break;
-			next = wstack[--sp];
-		}
-		node = next;
-	}
-	return blocked;
-}
-
 /* get_intersection of one given object (the inside-object shortcut,
  * reference render.c:143-144) and the geometric normal of a hit
  * (sphere outward object.c:258-261, triangle from winding

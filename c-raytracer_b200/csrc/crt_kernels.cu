@@ -11,11 +11,11 @@
  *     the reference's recursion becomes a per-lane stack of pending-ray records;
  *   - the >99 % of rays that are shadow rays are processed
  *     warp-cooperatively: the (shading point x light sample) index space of
- *     the warp's current shading points is flattened over the 32 lanes, so
- *     lanes stay full whatever the per-pixel ray budget is, neighbouring lanes
- *     trace rays from the same origin towards the same small light (coherent
- *     traversal), and the per-point sums come back with a fixed-order
- *     segmented warp reduction (deterministic image, no float atomics).
+ *     the warp's current shading points is flattened into a work list the 32
+ *     lanes pull from (dynamic refill), the any-hit walk is a sequence of
+ *     node / primitive unit steps scheduled by warp vote, and the per-point
+ *     sums are formed in a fixed order from per-ray slots (deterministic
+ *     image, no float atomics).
  */
 #include "crt_kernels.cuh"
 
@@ -150,12 +150,11 @@ __device__ __forceinline__ void flush_counters(const RenderParams &p, Counters &
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParams p)
+__global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(const RenderParams p)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	WarpShared *shared = reinterpret_cast<WarpShared *>(smem_raw);
-	float (*wslots)[3][kSlots] = reinterpret_cast<float (*)[3][kSlots]>(smem_raw + sizeof(WarpShared) * kWarpsPerBlock);
-	int *wqueue = reinterpret_cast<int *>(smem_raw + (sizeof(WarpShared) + sizeof(float) * 3 * kSlots) * kWarpsPerBlock);
+	int *wqueue = reinterpret_cast<int *>(smem_raw + sizeof(WarpShared) * kWarpsPerBlock);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp_local = threadIdx.x >> 5;
 	const uint32_t warp_global = blockIdx.x * kWarpsPerBlock + warp_local;
@@ -311,17 +310,19 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParam
 			 * The (lit shading point x light sample) index space of the warp is cut
 			 * into chunks of <= kSlots shadow rays.  Inside a chunk the lanes pull
 			 * ray indices from a warp counter: a lane whose any-hit walk ends takes
-			 * the next ray as soon as fewer than kRefill lanes are still walking,
-			 * so long walks (through the glass mesh) do not idle the lanes of short
-			 * ones (SIMT efficiency of the walk: 6/32 -> see profiles/).  Every ray
-			 * writes its contribution to its own slot and the slots of a point are
-			 * summed in a fixed order afterwards: the image does not depend on which
-			 * lane traced which ray. ------------------------------------------------ */
+			 * the next ray as soon as fewer than kRefill lanes are still walking, so
+			 * long walks (through the glass mesh) do not idle the lanes of short
+			 * ones.  The walk itself is split into unit steps the warp votes on
+			 * (crt_device.cuh, ShadowWalk).  Every ray writes its contribution to its
+			 * own slot and the slots of a point are summed in a fixed order
+			 * afterwards: the image does not depend on which lane traced which ray,
+			 * so frames are bit-reproducible whatever the schedule or GPU count. --- */
 			float sum_r = 0.f, sum_g = 0.f, sum_b = 0.f;
 			const uint32_t npts = (uint32_t)__popc(lit_mask);
 			const uint32_t L = sc.total_lights;
 			if (npts > 0u && L > 0u) {
-				float *slot_r = wslots[warp_local][0], *slot_g = wslots[warp_local][1], *slot_b = wslots[warp_local][2];
+				/* contribution slots: this warp's private scratch in global memory (stays in L2) */
+				float *slot_r = p.slots + (size_t)warp_global * (3 * kSlots), *slot_g = slot_r + kSlots, *slot_b = slot_g + kSlots;
 				const uint32_t pts_per_chunk = (uint32_t)kSlots / L; /* 0: a point spans several chunks */
 				uint32_t p0 = 0, s0 = 0;
 				while (p0 < npts) {
@@ -439,17 +440,20 @@ __global__ void __launch_bounds__(kBlockThreads) render_kernel(const RenderParam
 						const uint32_t keep = next < nwork ? (uint32_t)kRefill : 1u;
 						for (;;) {
 							const bool ci = have && shadow_can_inner(sw), cp = have && shadow_can_prim(sw);
-							const uint32_t ni = (uint32_t)__popc(__ballot_sync(kFull, ci));
-							const uint32_t np = (uint32_t)__popc(__ballot_sync(kFull, cp));
-							if (ni >= np) {
-								if (ci)
+							const unsigned bi = __ballot_sync(kFull, ci), bp = __ballot_sync(kFull, cp);
+							if ((uint32_t)__popc(bi | bp) < keep)
+								break; /* a lane is busy iff it can take one of the two steps */
+							if (__popc(bi) >= __popc(bp)) {
+								/* inner steps outnumber prim steps about 3:1: take two per vote */
+								if (ci) {
 									shadow_inner_step<COUNT>(sc, sr, rb, dist, sw, stack, q, cn);
+									if (shadow_can_inner(sw))
+										shadow_inner_step<COUNT>(sc, sr, rb, dist, sw, stack, q, cn);
+								}
 							} else {
 								if (cp)
 									shadow_prim_step<COUNT>(sc, sr, dist, em_object, sw, q, blocked, ir, ig, ib, cn);
 							}
-							if ((uint32_t)__popc(__ballot_sync(kFull, have && shadow_walk_busy(sw))) < keep)
-								break;
 						}
 						/* lanes whose walk ended are retired at the top of the loop */
 					}
@@ -681,7 +685,7 @@ void launch_raygen_rows(const crt_render_opts &o, float *row_pos, cudaStream_t s
 	raygen_rows_kernel<<<(o.height + threads - 1) / threads, threads, 0, stream>>>(o, row_pos);
 }
 
-constexpr size_t kRenderSmem = (sizeof(WarpShared) + sizeof(float) * 3 * kSlots + sizeof(int) * kLeafQueue * 32) * kWarpsPerBlock;
+constexpr size_t kRenderSmem = (sizeof(WarpShared) + sizeof(int) * kLeafQueue * 32) * kWarpsPerBlock;
 
 int render_blocks_per_sm(bool count)
 {

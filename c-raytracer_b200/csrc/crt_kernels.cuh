@@ -14,8 +14,11 @@ constexpr int kChunkTiles = 8;             /* sharding granularity (crt_render_o
 constexpr int kWarpsPerBlock = 8;
 constexpr int kBlockThreads = kWarpsPerBlock * 32;
 constexpr int kNumCounters = 11;
+#ifndef CRT_MIN_BLOCKS
+#define CRT_MIN_BLOCKS 2                   /* resident render blocks per SM the register budget is set for */
+#endif
 constexpr int kPendingWords = 13;          /* words per pending-ray record */
-constexpr int kSlots = 640;                /* shadow-ray contribution slots per warp (one chunk) */
+constexpr int kSlots = 1024;               /* shadow-ray contribution slots per warp (one chunk) */
 constexpr int kRefill = 20;                /* lanes fetch new shadow rays when fewer than this many are walking */
 
 struct RenderParams {
@@ -29,6 +32,7 @@ struct RenderParams {
 	unsigned int *tile_counter;
 	unsigned long long *counters;   /* kNumCounters, instrumented instance only */
 	float *pending;                 /* per-lane pending-ray stacks */
+	float *slots;                   /* per-warp shadow-ray contribution slots: 3 * kSlots floats each */
 	uint32_t pending_depth;
 };
 

@@ -10,7 +10,8 @@ import numpy as np
 from . import _abi
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "csrc", "libcrt.so")
+# CRT_LIBCRT: build-variant override used by tools/ experiments only
+LIB_PATH = os.environ.get("CRT_LIBCRT") or os.path.join(HERE, "csrc", "libcrt.so")
 
 # every symbol include/crt.h declares
 SYMBOLS = [
