@@ -177,7 +177,7 @@ def ours(a):
 
     import _pkg
     _pkg.load()
-    from c_raytracer_b200 import _abi, device, host
+    from c_raytracer_b200 import _abi, device, host, multigpu
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -202,7 +202,7 @@ def ours(a):
 
     def make_opts(count=False):
         o = scene.options(W, H, *engine_flags(a))
-        o.shard_index, o.shard_count = rank, world
+        multigpu.shard_options(o, rank, world)
         if count:
             o.flags |= _abi.CRT_RENDER_COUNT_STATS
         return o
@@ -236,9 +236,7 @@ def ours(a):
         """one frame, framebuffer left on rank 0's device"""
         flush.zero_()  # L2 flush between steps (outside the kernel's own events)
         dev.render_device(opts, d_raster.data_ptr(), d_z.data_ptr(), stream.cuda_stream)
-        if world > 1:
-            dist.reduce(d_raster, 0, op=dist.ReduceOp.SUM)
-            dist.reduce(d_z, 0, op=dist.ReduceOp.SUM)
+        multigpu.assemble(d_raster, d_z, 0)  # N > 1: NCCL reduce(sum) of the disjoint shards onto rank 0
 
     # ---- device-resident timing ---------------------------------------------------
     for _ in range(a.warmup):

@@ -9,8 +9,8 @@
 
 namespace crt {
 
-constexpr int kTileW = 8, kTileH = 4;      /* one warp owns an 8x4 pixel tile: lane = pixel */
-constexpr int kChunkTiles = 8;             /* sharding granularity (crt_render_opts.shard_*) */
+constexpr int kTileW = CRT_TILE_W, kTileH = CRT_TILE_H;      /* one warp owns an 8x4 pixel tile: lane = pixel */
+constexpr int kChunkTiles = CRT_SHARD_CHUNK_TILES;            /* sharding granularity (crt_render_opts.shard_*) */
 constexpr int kWarpsPerBlock = 8;
 constexpr int kBlockThreads = kWarpsPerBlock * 32;
 constexpr int kNumCounters = 11;

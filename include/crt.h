@@ -145,6 +145,14 @@ enum crt_attenuation { CRT_ATTEN_NONE = 0, CRT_ATTEN_LINEAR = 1, CRT_ATTEN_SQUAR
 
 #define CRT_RENDER_COUNT_STATS 1u /* run the instrumented kernel (ray / test counters) */
 
+/* Frame partition used for multi-GPU sharding (crt_render_opts.shard_*): the
+ * frame is cut into CRT_TILE_W x CRT_TILE_H pixel tiles, numbered row-major over
+ * ceil(W / CRT_TILE_W) columns; CRT_SHARD_CHUNK_TILES consecutive tiles form a
+ * chunk; chunk k belongs to shard k % shard_count. */
+#define CRT_TILE_W 8
+#define CRT_TILE_H 4
+#define CRT_SHARD_CHUNK_TILES 8
+
 /*
  * Per-frame parameters: the image plane `struct Image` (image.h:17-26, set up
  * by image_init image.c:34-56), `camera.position` (camera.h:17-22) and the

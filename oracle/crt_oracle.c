@@ -751,6 +751,8 @@ int oracle_render(const oracle_scene *sc, const crt_render_opts *o, float *raste
 	memset(z_buffer, 0, pixels * sizeof(float));
 	uint64_t n_closest = 0, n_shadow = 0, n_shaded = 0;
 	const v3 kr = { 1.f, 1.f, 1.f };
+	const uint32_t shards = o->shard_count ? o->shard_count : 1u;
+	const uint32_t tiles_x = (o->width + CRT_TILE_W - 1) / CRT_TILE_W;
 #pragma omp parallel for schedule(dynamic, 1) reduction(+ : n_closest, n_shadow, n_shaded)
 	for (uint32_t row = 0; row < o->height; row++) {
 		struct or_counters cnt = { 0, 0, 0 };
@@ -761,6 +763,12 @@ int oracle_render(const oracle_scene *sc, const crt_render_opts *o, float *raste
 		uint32_t pixel = o->width * row;
 		for (uint32_t col = 0; col < o->width; col++, pixel++) {
 			add3v(pos, o->vx, pos);
+			if (shards > 1) {
+				/* frame partition of include/crt.h: tile -> chunk -> shard */
+				const uint32_t tile = (row / CRT_TILE_H) * tiles_x + col / CRT_TILE_W;
+				if ((tile / CRT_SHARD_CHUNK_TILES) % shards != o->shard_index)
+					continue;
+			}
 			sub3v(pos, o->cam_pos, dir);
 			norm3(dir);
 			z_buffer[pixel] = cast_ray(&cx, o->cam_pos, dir, kr, raster + 3 * (size_t)pixel, o->max_bounces, -1,

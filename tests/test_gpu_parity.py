@@ -304,6 +304,18 @@ def test_full_geometry_small_frame_vs_oracle(gpu, scene, flags):
     assert abs(int(st.rays_shadow) - int(ost.rays_shadow)) <= 1e-3 * ost.rays_shadow
 
 
+def test_shard_partition_matches_host_logic(gpu):
+    """The pixels a shard renders are those multigpu.shard_of_pixels() assigns to it."""
+    from c_raytracer_b200 import multigpu
+    sc, dev = dev_scene("scene3")  # closed box: every pixel hits something
+    w, h = 203, 77
+    owner = multigpu.shard_of_pixels(w, h, 3).numpy()
+    for k in range(3):
+        o = multigpu.shard_options(sc.options(w, h), k, 3)
+        _, z = dev.render(o)
+        np.testing.assert_array_equal(z > 0, owner == k)
+
+
 def test_seed_changes_only_the_noise(gpu):
     sc, dev = dev_scene("scene1")
     a, za = dev.render(sc.options(320, 180, "--seed", "1"))
