@@ -186,6 +186,8 @@ def ours(a):
         raise RuntimeError("bench.py: no CUDA device -- the trace loop has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner out of stdout: one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -231,12 +233,18 @@ def ours(a):
     total_flops = _abi.algorithmic_flops(tot)
 
     opts = make_opts()
+    asm_events = []
+    ev_a0, ev_a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
     def step_device():
         """one frame, framebuffer left on rank 0's device"""
         flush.zero_()  # L2 flush between steps (outside the kernel's own events)
         dev.render_device(opts, d_raster.data_ptr(), d_z.data_ptr(), stream.cuda_stream)
-        multigpu.assemble(d_raster, d_z, 0)  # N > 1: NCCL reduce(sum) of the disjoint shards onto rank 0
+        if world > 1:
+            ev_a0.record()
+            multigpu.assemble(d_raster, d_z, 0)  # NCCL reduce(sum) of the disjoint shards onto rank 0
+            ev_a1.record()
+            asm_events.append((ev_a0, ev_a1))
 
     # ---- device-resident timing ---------------------------------------------------
     for _ in range(a.warmup):
@@ -264,6 +272,7 @@ def ours(a):
     if world > 1:
         dist.all_reduce(elapsed, op=dist.ReduceOp.MAX)
     total_ms, kernel_avg_ms = float(elapsed[0]), float(elapsed[1])
+    assemble_ms = ev_a0.elapsed_time(ev_a1) if world > 1 else 0.0  # last frame's assembly, incl. waiting for the slowest rank
     ms_per_step = total_ms / a.steps
     value = total_rays / (ms_per_step * 1e-3) / 1e6
 
@@ -325,7 +334,7 @@ def ours(a):
             "rays_per_frame": total_rays, "rays_closest": tot.rays_closest, "rays_shadow": tot.rays_shadow,
             "l2": "flushed between steps (256 MiB memset)", "parallelism": f"tile-chunk round-robin x{world}, scene replicated",
             "bvh_nodes": info.num_nodes, "bvh_build_ms": info.build_ms, "scene_upload_ms": info.upload_ms,
-            "scene_setup_s": setup_s, "seed": 1,
+            "scene_setup_s": setup_s, "seed": 1, "assemble_ms": assemble_ms,
         },
         "ms_per_frame": ms_per_step,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_frame": float(e2e_ms[0]),

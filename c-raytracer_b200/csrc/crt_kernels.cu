@@ -166,17 +166,29 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 
 	for (;;) {
 		/* ---- next tile of this shard ------------------------------------- */
-		uint32_t local_tile = 0;
+		/* work unit: a whole 8x4 tile, or -- for the last tiles of the queue, so
+		 * that the frame does not end on a few warps finishing multi-100-ms tiles --
+		 * one 8-pixel row of a tile (lanes 0..7).  A pixel's value does not depend
+		 * on the shape of the unit it is traced in. */
+		uint32_t unit = 0;
 		if (lane == 0)
-			local_tile = atomicAdd(p.tile_counter, 1u);
-		local_tile = __shfl_sync(kFull, local_tile, 0);
-		if (local_tile >= p.num_local_tiles)
+			unit = atomicAdd(p.tile_counter, 1u);
+		unit = __shfl_sync(kFull, unit, 0);
+		if (unit >= p.num_units)
 			break;
+		uint32_t local_tile = unit, pix_lane = lane;
+		bool lane_on = true;
+		if (unit >= p.fine_from) {
+			const uint32_t v = unit - p.fine_from;
+			local_tile = p.fine_from + v / (uint32_t)kTileH;
+			pix_lane = (v % (uint32_t)kTileH) * (uint32_t)kTileW + lane;
+			lane_on = lane < (uint32_t)kTileW;
+		}
 		const uint32_t chunk = (local_tile / kChunkTiles) * o.shard_count + o.shard_index;
 		const uint32_t tile = chunk * kChunkTiles + local_tile % kChunkTiles;
 		const uint32_t tx = tile % p.tiles_x, ty = tile / p.tiles_x;
-		const uint32_t px = tx * kTileW + (lane & 7u), py = ty * kTileH + (lane >> 3);
-		const bool in_image = ty < p.tiles_y && px < o.width && py < o.height;
+		const uint32_t px = tx * kTileW + (pix_lane & 7u), py = ty * kTileH + (pix_lane >> 3);
+		const bool in_image = lane_on && ty < p.tiles_y && px < o.width && py < o.height;
 		const uint32_t pixel = py * o.width + px;
 
 		float acc_r = 0.f, acc_g = 0.f, acc_b = 0.f, z_value = 0.f;

@@ -29,6 +29,8 @@ struct RenderParams {
 	const float *row_pos;           /* W*H*3: running-sum pixel positions (raygen_rows_kernel) */
 	uint32_t tiles_x, tiles_y;
 	uint32_t num_local_tiles;       /* tiles of this shard */
+	uint32_t fine_from;             /* local tiles from this index on are handed out as 8-pixel rows */
+	uint32_t num_units;             /* work units: fine_from + (num_local_tiles - fine_from) * kTileH */
 	unsigned int *tile_counter;
 	unsigned long long *counters;   /* kNumCounters, instrumented instance only */
 	float *pending;                 /* per-lane pending-ray stacks */
