@@ -449,22 +449,29 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 							break;
 						/* -- walk until fewer than `keep` lanes are still walking: each
 						 * iteration the warp takes the kind of step more lanes are ready for */
-						const uint32_t keep = next < nwork ? (uint32_t)kRefill : 1u;
+						const uint32_t keep = next < nwork ? p.refill : 1u;
 						for (;;) {
 							const bool ci = have && shadow_can_inner(sw), cp = have && shadow_can_prim(sw);
 							const unsigned bi = __ballot_sync(kFull, ci), bp = __ballot_sync(kFull, cp);
 							if ((uint32_t)__popc(bi | bp) < keep)
 								break; /* a lane is busy iff it can take one of the two steps */
 							if (__popc(bi) >= __popc(bp)) {
-								/* inner steps outnumber prim steps about 3:1: take two per vote */
+								/* inner steps outnumber prim steps about 3:1: up to kInnerPerVote per vote */
 								if (ci) {
 									shadow_inner_step<COUNT>(sc, sr, rb, dist, sw, stack, q, cn);
-									if (shadow_can_inner(sw))
-										shadow_inner_step<COUNT>(sc, sr, rb, dist, sw, stack, q, cn);
+#pragma unroll
+									for (int k = 1; k < kInnerPerVote; k++)
+										if (shadow_can_inner(sw))
+											shadow_inner_step<COUNT>(sc, sr, rb, dist, sw, stack, q, cn);
 								}
 							} else {
-								if (cp)
+								if (cp) {
 									shadow_prim_step<COUNT>(sc, sr, dist, em_object, sw, q, blocked, ir, ig, ib, cn);
+#pragma unroll
+									for (int k = 1; k < kPrimPerVote; k++)
+										if (shadow_can_prim(sw))
+											shadow_prim_step<COUNT>(sc, sr, dist, em_object, sw, q, blocked, ir, ig, ib, cn);
+								}
 							}
 						}
 						/* lanes whose walk ended are retired at the top of the loop */

@@ -13,13 +13,20 @@ constexpr int kTileW = CRT_TILE_W, kTileH = CRT_TILE_H;      /* one warp owns an
 constexpr int kChunkTiles = CRT_SHARD_CHUNK_TILES;            /* sharding granularity (crt_render_opts.shard_*) */
 constexpr int kWarpsPerBlock = 8;
 constexpr int kBlockThreads = kWarpsPerBlock * 32;
+#ifndef CRT_INNER_PER_VOTE
+#define CRT_INNER_PER_VOTE 4
+#endif
+#ifndef CRT_PRIM_PER_VOTE
+#define CRT_PRIM_PER_VOTE 2
+#endif
+constexpr int kInnerPerVote = CRT_INNER_PER_VOTE, kPrimPerVote = CRT_PRIM_PER_VOTE; /* unit steps per warp vote */
 constexpr int kNumCounters = 11;
 #ifndef CRT_MIN_BLOCKS
 #define CRT_MIN_BLOCKS 2                   /* resident render blocks per SM the register budget is set for */
 #endif
 constexpr int kPendingWords = 13;          /* words per pending-ray record */
 constexpr int kSlots = 1024;               /* shadow-ray contribution slots per warp (one chunk) */
-constexpr int kRefill = 20;                /* lanes fetch new shadow rays when fewer than this many are walking */
+constexpr int kRefill = 8;                 /* lanes fetch new shadow rays when fewer than this many are walking */
 
 struct RenderParams {
 	DScene sc;
@@ -29,6 +36,7 @@ struct RenderParams {
 	const float *row_pos;           /* W*H*3: running-sum pixel positions (raygen_rows_kernel) */
 	uint32_t tiles_x, tiles_y;
 	uint32_t num_local_tiles;       /* tiles of this shard */
+	uint32_t refill;                /* lanes fetch new shadow rays when fewer than this many are walking */
 	uint32_t fine_from;             /* local tiles from this index on are handed out as 8-pixel rows */
 	uint32_t num_units;             /* work units: fine_from + (num_local_tiles - fine_from) * kTileH */
 	unsigned int *tile_counter;
