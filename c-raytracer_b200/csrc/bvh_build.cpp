@@ -226,4 +226,229 @@ void build_bvh(const std::vector<Aabb> &boxes, BvhResult &out)
 	out.max_depth = B.max_depth;
 }
 
+/* ---- 8-wide collapse ------------------------------------------------------ */
+
+namespace {
+
+struct WideRef {
+	int32_t ref; /* binary node index, or encoded leaf */
+	Aabb box;
+	uint32_t first, count;
+};
+
+struct WideBuilder {
+	const BvhResult &bvh;
+	WideResult &out;
+	std::vector<uint32_t> first, count; /* primitive range of every binary node */
+	uint32_t merge_prims = 0;            /* binary subtrees with at most this many primitives become one leaf */
+};
+
+void decode_leaf(int32_t ref, uint32_t &first, uint32_t &count)
+{
+	const uint32_t leaf = static_cast<uint32_t>(~ref);
+	first = leaf >> kLeafCountBits;
+	count = (leaf & ((1u << kLeafCountBits) - 1u)) + 1u;
+}
+
+Aabb child_box(const BvhNode &n, int which)
+{
+	const float *xy = which == 0 ? n.xy0 : n.xy1;
+	Aabb b;
+	b.lo[0] = xy[0];
+	b.hi[0] = xy[1];
+	b.lo[1] = xy[2];
+	b.hi[1] = xy[3];
+	b.lo[2] = n.z01[2 * which + 0];
+	b.hi[2] = n.z01[2 * which + 1];
+	return b;
+}
+
+void ranges(WideBuilder &W, int32_t node)
+{
+	uint32_t lo = 0xffffffffu, total = 0;
+	for (int c = 0; c < 2; c++) {
+		const int32_t ref = W.bvh.nodes[node].child[c];
+		uint32_t f, n;
+		if (ref < 0) {
+			decode_leaf(ref, f, n);
+			if (child_box(W.bvh.nodes[node], c).lo[0] >= 1e30f)
+				continue; /* the absent child of a one-leaf scene */
+		} else {
+			ranges(W, ref);
+			f = W.first[ref];
+			n = W.count[ref];
+		}
+		lo = std::min(lo, f);
+		total += n;
+	}
+	W.first[node] = lo;
+	W.count[node] = total;
+}
+
+WideRef make_ref(WideBuilder &W, int32_t node, int which)
+{
+	WideRef r;
+	r.ref = W.bvh.nodes[node].child[which];
+	r.box = child_box(W.bvh.nodes[node], which);
+	if (r.ref < 0) {
+		decode_leaf(r.ref, r.first, r.count);
+	} else {
+		r.first = W.first[r.ref];
+		r.count = W.count[r.ref];
+	}
+	return r;
+}
+
+int32_t wide_node(WideBuilder &W, int32_t node, uint32_t depth)
+{
+	W.out.max_depth = std::max(W.out.max_depth, depth);
+	const int32_t id = static_cast<int32_t>(W.out.nodes.size());
+	W.out.nodes.emplace_back();
+	std::vector<WideRef> kids;
+	for (int c = 0; c < 2; c++) {
+		const WideRef r = make_ref(W, node, c);
+		if (!(r.ref < 0 && r.box.lo[0] >= 1e30f))
+			kids.push_back(r);
+	}
+	/* open the binary child with the largest surface that is too big for a wide leaf */
+	while (kids.size() < 8) {
+		int best = -1;
+		float best_area = -1.f;
+		for (size_t i = 0; i < kids.size(); i++)
+			if (kids[i].ref >= 0 && kids[i].count > W.merge_prims && half_area(kids[i].box) > best_area) {
+				best_area = half_area(kids[i].box);
+				best = static_cast<int>(i);
+			}
+		if (best < 0)
+			break;
+		const int32_t open = kids[best].ref;
+		kids[best] = make_ref(W, open, 0);
+		kids.push_back(make_ref(W, open, 1));
+	}
+	for (int j = 0; j < 8; j++) {
+		int32_t code = kWideEmpty;
+		Aabb box;
+		for (int k = 0; k < 3; k++)
+			box.lo[k] = box.hi[k] = 1e30f;
+		if (j < static_cast<int>(kids.size())) {
+			const WideRef &r = kids[j];
+			box = r.box;
+			if (r.ref < 0 || r.count <= W.merge_prims)
+				code = encode_leaf(r.first, r.count); /* a whole small subtree becomes one leaf */
+			else
+				code = wide_node(W, r.ref, depth + 1);
+		}
+		WideNode &n = W.out.nodes[id]; /* re-fetch: the vector may have grown */
+		n.a[j][0] = box.lo[0];
+		n.a[j][1] = box.lo[1];
+		n.a[j][2] = box.lo[2];
+		n.a[j][3] = box.hi[0];
+		n.b[j][0] = box.hi[1];
+		n.b[j][1] = box.hi[2];
+		std::memcpy(&n.b[j][2], &code, sizeof code);
+		n.b[j][3] = 0.f;
+	}
+	return id;
+}
+
+} // namespace
+
+void build_wide(const BvhResult &bvh, WideResult &out, uint32_t merge_prims)
+{
+	out.nodes.clear();
+	out.max_depth = 0;
+	if (bvh.nodes.empty())
+		return;
+	WideBuilder W{ bvh, out, {}, {}, std::min(merge_prims, kWideLeafPrims) };
+	W.first.assign(bvh.nodes.size(), 0);
+	W.count.assign(bvh.nodes.size(), 0);
+	ranges(W, 0);
+	out.nodes.reserve(bvh.nodes.size() / 2 + 1);
+	wide_node(W, 0, 1);
+}
+
+
+/* ---- quantisation of the 8-wide nodes ----------------------------------------- */
+
+namespace {
+
+/* smallest power of two s with extent <= 255 * s, as an IEEE exponent byte */
+uint32_t scale_exponent(float extent)
+{
+	if (!(extent > 0.f))
+		return 1u; /* 2^-126: all planes quantise to 0 */
+	int e;
+	std::frexp(extent / 255.f, &e); /* extent / 255 = m * 2^e, m in [0.5, 1) => 2^e >= extent / 255 */
+	const int biased = std::min(std::max(e + 127, 1), 254);
+	return static_cast<uint32_t>(biased);
+}
+
+float exponent_scale(uint32_t biased)
+{
+	const uint32_t bits = biased << 23;
+	float f;
+	std::memcpy(&f, &bits, 4);
+	return f;
+}
+
+} // namespace
+
+void quantize_wide(const WideResult &wide, std::vector<QuantNode> &out)
+{
+	out.resize(wide.nodes.size());
+	for (size_t n = 0; n < wide.nodes.size(); n++) {
+		const WideNode &w = wide.nodes[n];
+		QuantNode &qn = out[n];
+		std::memset(&qn, 0, sizeof qn);
+		float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+		int32_t code[8];
+		float clo[8][3], chi[8][3];
+		for (int j = 0; j < 8; j++) {
+			std::memcpy(&code[j], &w.b[j][2], 4);
+			clo[j][0] = w.a[j][0]; clo[j][1] = w.a[j][1]; clo[j][2] = w.a[j][2];
+			chi[j][0] = w.a[j][3]; chi[j][1] = w.b[j][0]; chi[j][2] = w.b[j][1];
+			if (code[j] == kWideEmpty)
+				continue;
+			for (int k = 0; k < 3; k++) {
+				lo[k] = std::min(lo[k], clo[j][k]);
+				hi[k] = std::max(hi[k], chi[j][k]);
+			}
+		}
+		uint32_t ebits = 0;
+		float scale[3];
+		for (int k = 0; k < 3; k++) {
+			if (lo[k] > hi[k])
+				lo[k] = hi[k] = 0.f;
+			qn.origin[k] = lo[k];
+			uint32_t e = scale_exponent(hi[k] - lo[k]);
+			/* origin + 255 * scale must reach hi in FP32 arithmetic */
+			while (e < 254u && qn.origin[k] + 255.f * exponent_scale(e) < hi[k])
+				e++;
+			scale[k] = exponent_scale(e);
+			ebits |= e << (8 * k);
+		}
+		qn.exponents = ebits;
+		for (int j = 0; j < 8; j++) {
+			qn.code[j] = code[j];
+			for (int k = 0; k < 3; k++) {
+				uint8_t ql = 255, qh = 0; /* empty child: inverted, never hit */
+				if (code[j] != kWideEmpty) {
+					int a = static_cast<int>(std::floor((clo[j][k] - qn.origin[k]) / scale[k]));
+					a = std::min(std::max(a, 0), 255);
+					while (a > 0 && qn.origin[k] + static_cast<float>(a) * scale[k] > clo[j][k])
+						a--;
+					int b = static_cast<int>(std::ceil((chi[j][k] - qn.origin[k]) / scale[k]));
+					b = std::min(std::max(b, 0), 255);
+					while (b < 255 && qn.origin[k] + static_cast<float>(b) * scale[k] < chi[j][k])
+						b++;
+					ql = static_cast<uint8_t>(a);
+					qh = static_cast<uint8_t>(b);
+				}
+				qn.q[k][0][j] = ql;
+				qn.q[k][1][j] = qh;
+			}
+		}
+	}
+}
+
 } // namespace crt

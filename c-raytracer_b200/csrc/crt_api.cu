@@ -268,6 +268,18 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 	}
 	BvhResult bvh;
 	build_bvh(boxes, bvh);
+	/* the shadow walk's tree: 8-wide collapse of the binary tree, quantised child boxes */
+	WideResult wide;
+	uint32_t merge_prims = 0;
+	if (const char *e = std::getenv("CRT_WIDE_MERGE"))
+		merge_prims = static_cast<uint32_t>(std::max(0, std::atoi(e)));
+	build_wide(bvh, wide, merge_prims);
+	std::vector<QuantNode> qnodes;
+	quantize_wide(wide, qnodes);
+	if (bvh.max_depth + 1u > static_cast<uint32_t>(kStackSize) || 7u * wide.max_depth + 1u > static_cast<uint32_t>(kStackSize)) {
+		delete s;
+		return fail(CRT_ERR_UNSUPPORTED, "BVH too deep for the device stacks (binary %u, wide %u levels)", bvh.max_depth, wide.max_depth);
+	}
 	s->info.build_ms = now_ms() - t0;
 
 	/* ---- primitive records in leaf order ---------------------------------- */
@@ -299,7 +311,11 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 	std::vector<float4> nodes(4 * bvh.nodes.size());
 	if (!bvh.nodes.empty())
 		std::memcpy(nodes.data(), bvh.nodes.data(), bvh.nodes.size() * sizeof(BvhNode));
+	std::vector<float4> wide_nodes(6 * qnodes.size());
+	if (!qnodes.empty())
+		std::memcpy(wide_nodes.data(), qnodes.data(), qnodes.size() * sizeof(QuantNode));
 	rc = upload(s, nodes, &s->d.nodes);
+	if (!rc) rc = upload(s, wide_nodes, &s->d.wide);
 	if (!rc) rc = upload(s, prims, &s->d.prims);
 	if (!rc) rc = upload(s, normals, &s->d.normals);
 	if (!rc) rc = upload(s, planes, &s->d.planes);

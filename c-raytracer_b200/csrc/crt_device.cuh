@@ -33,7 +33,7 @@ constexpr uint32_t PRIM_SPHERE = 0x80000000u;
 constexpr uint32_t PRIM_TRANSPARENT = 0x40000000u;
 constexpr uint32_t PRIM_MATERIAL_MASK = 0x00ffffffu;
 
-constexpr int kStackSize = 64;          /* bvh_build.cpp bounds the depth below this */
+constexpr int kStackSize = 128;         /* >= binary tree depth (closest hit) and 7 * wide tree depth + 1 (shadow walk): checked at scene creation */
 constexpr int kStackSentinel = 0x7fffffff;
 constexpr int kLeafBits = 3;
 constexpr float kPi = 3.1415927f;       /* reference src/core/type.h:30 */
@@ -52,6 +52,7 @@ struct DEmitter {
 
 struct DScene {
 	const float4 *nodes;
+	const float4 *wide;  /* quantised 8-wide nodes of the shadow walk, 6 float4 each (bvh_build.h QuantNode) */
 	const float4 *prims;
 	const float4 *normals;
 	const float4 *planes;
@@ -409,11 +410,12 @@ __device__ __forceinline__ bool shadow_planes(const DScene &sc, const Ray &r, fl
  * primitive of the queued leaves).  The render kernel lets the warp vote each
  * iteration for the kind more lanes are ready for, instead of a while-while
  * loop in which lanes at a leaf wait for the longest descent of the warp. */
-constexpr int kLeafQueue = 8; /* queued leaf codes per lane (shared memory, [slot][lane]) */
+constexpr int kLeafQueue = 16; /* queued leaf codes per lane ([slot][lane]); a node step adds up to 8 */
 
 struct ShadowWalk {
-	int node;       /* next inner node, kStackSentinel: none */
-	int sp;         /* stack[0] = kStackSentinel */
+	int node;       /* wide node to visit next, kStackSentinel: none */
+	int top;        /* top of the stack, kept in a register: a pop's load is only needed by the NEXT pop */
+	int sp;         /* entries in stack[] below top */
 	int leaf_first; /* primitive slot being tested next */
 	int leaf_left;  /* primitives left in the current leaf */
 	int qhead, qcount;
@@ -422,6 +424,7 @@ struct ShadowWalk {
 __device__ __forceinline__ void shadow_walk_reset(ShadowWalk &w)
 {
 	w.node = kStackSentinel;
+	w.top = kStackSentinel;
 	w.sp = 0;
 	w.leaf_first = 0;
 	w.leaf_left = 0;
@@ -436,7 +439,7 @@ __device__ __forceinline__ bool shadow_walk_busy(const ShadowWalk &w)
 
 __device__ __forceinline__ bool shadow_can_inner(const ShadowWalk &w)
 {
-	return w.node != kStackSentinel && w.qcount <= kLeafQueue - 2;
+	return w.node != kStackSentinel && w.qcount <= kLeafQueue - 8;
 }
 
 __device__ __forceinline__ bool shadow_can_prim(const ShadowWalk &w)
@@ -444,49 +447,82 @@ __device__ __forceinline__ bool shadow_can_prim(const ShadowWalk &w)
 	return w.leaf_left > 0 || w.qcount > 0;
 }
 
-/* queue: this lane's column of q[kLeafQueue][32] */
-template <bool COUNT>
-__device__ __forceinline__ void shadow_inner_step(const DScene &sc, const Ray &r, const RayBox &rb, float dist, ShadowWalk &w,
-	int *stack, int *q, Counters &cn)
+/* 1/d with a floor on |d|: keeps the quantised slab arithmetic finite (no 0 * inf) and
+ * still puts both planes of an axis at -+huge for an axis-parallel ray */
+__device__ __forceinline__ float safe_rcp(float d)
 {
-	const float4 *n = sc.nodes + 4 * w.node;
-	const float4 xy0 = ldg4(n), xy1 = ldg4(n + 1), z01 = ldg4(n + 2);
-	const float4 ch = ldg4(n + 3);
-	bool h0, h1;
-	float t0, t1;
-	test_children(xy0, xy1, z01, r, rb, dist, h0, h1, t0, t1);
-	Cnt<COUNT>::add(cn.box, 2u);
-	const int c0 = __float_as_int(ch.x), c1 = __float_as_int(ch.y);
-	int next = kStackSentinel;
-	if (h0) {
-		if (c0 < 0) {
-			q[((w.qhead + w.qcount) & (kLeafQueue - 1)) * 32] = c0;
-			w.qcount++;
-		} else {
-			next = c0;
-		}
-	}
-	if (h1) {
-		if (c1 < 0) {
-			q[((w.qhead + w.qcount) & (kLeafQueue - 1)) * 32] = c1;
-			w.qcount++;
-		} else if (next == kStackSentinel) {
-			next = c1;
-		} else {
-			stack[w.sp++] = c1;
-		}
-	}
-	if (next == kStackSentinel)
-		next = stack[--w.sp]; /* stack[0] is the sentinel */
-	w.node = next;
+	return 1.f / (fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d));
 }
 
-template <bool COUNT>
+/* ray constants of the wide walk: idir, and per-axis byte selectors are derived per node */
+struct RayWide {
+	float idx, idy, idz;
+};
+
+/* float(byte k of word) without a conversion instruction: place the byte in the mantissa of 2^23 */
+__device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t selector)
+{
+	return __uint_as_float(__byte_perm(word, 0x4b000000u, selector)) - 8388608.f;
+}
+
+/* One visit of a quantised 8-wide node (bvh_build.h QuantNode): six vector loads,
+ * eight slab tests.  qstride: 32 for the render kernel's [slot][lane] queue, 1 for a
+ * private array. */
+template <bool COUNT, int QSTRIDE>
+__device__ __forceinline__ void shadow_inner_step(const DScene &sc, const Ray &r, const RayWide &rw, float dist, ShadowWalk &w,
+	int *stack, int *q, Counters &cn)
+{
+	const float4 *n = sc.wide + 6 * (size_t)w.node;
+	const float4 w0 = ldg4(n), w1 = ldg4(n + 1), w2 = ldg4(n + 2), w3 = ldg4(n + 3), w4 = ldg4(n + 4), w5 = ldg4(n + 5);
+	const uint32_t eb = __float_as_uint(w0.w);
+	const float adjx = __uint_as_float((eb & 0xffu) << 23) * rw.idx;
+	const float adjy = __uint_as_float(((eb >> 8) & 0xffu) << 23) * rw.idy;
+	const float adjz = __uint_as_float(((eb >> 16) & 0xffu) << 23) * rw.idz;
+	const float orgx = (w0.x - r.ox) * rw.idx, orgy = (w0.y - r.oy) * rw.idy, orgz = (w0.z - r.oz) * rw.idz;
+	/* near / far planes by the sign of the direction */
+	const bool nx = rw.idx < 0.f, ny = rw.idy < 0.f, nz = rw.idz < 0.f;
+	const uint32_t nearx[2] = { __float_as_uint(nx ? w1.z : w1.x), __float_as_uint(nx ? w1.w : w1.y) };
+	const uint32_t farx[2] = { __float_as_uint(nx ? w1.x : w1.z), __float_as_uint(nx ? w1.y : w1.w) };
+	const uint32_t neary[2] = { __float_as_uint(ny ? w2.z : w2.x), __float_as_uint(ny ? w2.w : w2.y) };
+	const uint32_t fary[2] = { __float_as_uint(ny ? w2.x : w2.z), __float_as_uint(ny ? w2.y : w2.w) };
+	const uint32_t nearz[2] = { __float_as_uint(nz ? w3.z : w3.x), __float_as_uint(nz ? w3.w : w3.y) };
+	const uint32_t farz[2] = { __float_as_uint(nz ? w3.x : w3.z), __float_as_uint(nz ? w3.y : w3.w) };
+	const int code[8] = { __float_as_int(w4.x), __float_as_int(w4.y), __float_as_int(w4.z), __float_as_int(w4.w),
+		__float_as_int(w5.x), __float_as_int(w5.y), __float_as_int(w5.z), __float_as_int(w5.w) };
+#pragma unroll
+	for (int i = 0; i < 8; i++) {
+		const uint32_t sel = 0x7540u + (uint32_t)(i & 3); /* bytes: (b_i, 0x00, 0x00, 0x4b) */
+		const float tnx = fmaf(byte_to_float(nearx[i >> 2], sel), adjx, orgx);
+		const float tny = fmaf(byte_to_float(neary[i >> 2], sel), adjy, orgy);
+		const float tnz = fmaf(byte_to_float(nearz[i >> 2], sel), adjz, orgz);
+		const float tfx = fmaf(byte_to_float(farx[i >> 2], sel), adjx, orgx);
+		const float tfy = fmaf(byte_to_float(fary[i >> 2], sel), adjy, orgy);
+		const float tfz = fmaf(byte_to_float(farz[i >> 2], sel), adjz, orgz);
+		const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
+		const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, dist));
+		if (code[i] != kStackSentinel)
+			Cnt<COUNT>::add(cn.box);
+		/* an empty child has near 255 / far 0 planes on every axis (and the sentinel code) */
+		if (tmin <= tmax && code[i] != kStackSentinel) {
+			if (code[i] >= 0) {
+				stack[w.sp++] = w.top;
+				w.top = code[i];
+			} else {
+				q[((w.qhead + w.qcount) & (kLeafQueue - 1)) * QSTRIDE] = code[i];
+				w.qcount++;
+			}
+		}
+	}
+	w.node = w.top;
+	w.top = w.sp > 0 ? stack[--w.sp] : kStackSentinel;
+}
+
+template <bool COUNT, int QSTRIDE>
 __device__ __forceinline__ void shadow_prim_step(const DScene &sc, const Ray &r, float dist, int emitter_object, ShadowWalk &w,
 	int *q, bool &blocked, float &lr, float &lg, float &lb, Counters &cn)
 {
 	if (w.leaf_left == 0) {
-		const int leaf = ~q[w.qhead * 32];
+		const int leaf = ~q[w.qhead * QSTRIDE];
 		w.qhead = (w.qhead + 1) & (kLeafQueue - 1);
 		w.qcount--;
 		w.leaf_first = leaf >> kLeafBits;
@@ -509,6 +545,32 @@ __device__ __forceinline__ void shadow_prim_step(const DScene &sc, const Ray &r,
 		lg *= __ldg(&m->kt[1]);
 		lb *= __ldg(&m->kt[2]);
 	}
+}
+
+/* is_light_blocked() through the production walk, one ray per thread (the
+ * crt_trace_shadow seam): planes, then node / primitive unit steps until done. */
+template <bool COUNT>
+__device__ __forceinline__ bool trace_shadow_wide(const DScene &sc, const Ray &r, float dist, int emitter_object,
+	float &lr, float &lg, float &lb, Counters &cn)
+{
+	if (shadow_planes<COUNT>(sc, r, dist, lr, lg, lb, cn))
+		return true;
+	if (sc.num_nodes == 0)
+		return false;
+	int stack[kStackSize];
+	int q[kLeafQueue];
+	ShadowWalk w;
+	shadow_walk_reset(w);
+	w.node = 0;
+	const RayWide rw = { safe_rcp(r.dx), safe_rcp(r.dy), safe_rcp(r.dz) };
+	bool blocked = false;
+	while (shadow_walk_busy(w)) {
+		if (shadow_can_inner(w))
+			shadow_inner_step<COUNT, 1>(sc, r, rw, dist, w, stack, q, cn);
+		else
+			shadow_prim_step<COUNT, 1>(sc, r, dist, emitter_object, w, q, blocked, lr, lg, lb, cn);
+	}
+	return blocked;
 }
 
 /* get_intersection of one given object (the inside-object shortcut,

@@ -352,7 +352,7 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 					bool have = false;
 					uint32_t w = 0, e_lane = 0;
 					Ray sr = { 0.f, 0.f, 0.f, 0.f, 0.f, 1.f };
-					RayBox rb = {};
+					RayWide rw = { 1.f, 1.f, 1.f };
 					float dist = 0.f, d2 = 0.f, ir = 0.f, ig = 0.f, ib = 0.f;
 					int em_object = -1;
 					bool blocked = false;
@@ -436,10 +436,10 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 									Cnt<COUNT>::add(cn.shadow);
 									blocked = shadow_planes<COUNT>(sc, sr, dist, ir, ig, ib, cn);
 									if (!blocked && sc.num_nodes != 0u) {
-										rb = make_raybox(sr);
-										stack[0] = kStackSentinel;
-										sw.sp = 1;
-										sw.node = 0;
+										rw.idx = safe_rcp(sr.dx);
+										rw.idy = safe_rcp(sr.dy);
+										rw.idz = safe_rcp(sr.dz);
+										sw.node = 0; /* root of the wide tree; stack and queue are empty */
 									}
 								}
 							}
@@ -455,23 +455,17 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 							const unsigned bi = __ballot_sync(kFull, ci), bp = __ballot_sync(kFull, cp);
 							if ((uint32_t)__popc(bi | bp) < keep)
 								break; /* a lane is busy iff it can take one of the two steps */
-							if (__popc(bi) >= __popc(bp)) {
-								/* inner steps outnumber prim steps about 3:1: up to kInnerPerVote per vote */
-								if (ci) {
-									shadow_inner_step<COUNT>(sc, sr, rb, dist, sw, stack, q, cn);
-#pragma unroll
-									for (int k = 1; k < kInnerPerVote; k++)
-										if (shadow_can_inner(sw))
-											shadow_inner_step<COUNT>(sc, sr, rb, dist, sw, stack, q, cn);
-								}
+							if (__popc(bi) * kInnerWeight >= __popc(bp) * kPrimWeight) {
+								/* several steps per vote; rolled loops keep the walk inside the instruction cache */
+#pragma unroll 1
+								for (int k = 0; k < kInnerPerVote; k++)
+									if (have && shadow_can_inner(sw))
+										shadow_inner_step<COUNT, 32>(sc, sr, rw, dist, sw, stack, q, cn);
 							} else {
-								if (cp) {
-									shadow_prim_step<COUNT>(sc, sr, dist, em_object, sw, q, blocked, ir, ig, ib, cn);
-#pragma unroll
-									for (int k = 1; k < kPrimPerVote; k++)
-										if (shadow_can_prim(sw))
-											shadow_prim_step<COUNT>(sc, sr, dist, em_object, sw, q, blocked, ir, ig, ib, cn);
-								}
+#pragma unroll 1
+								for (int k = 0; k < kPrimPerVote; k++)
+									if (have && shadow_can_prim(sw))
+										shadow_prim_step<COUNT, 32>(sc, sr, dist, em_object, sw, q, blocked, ir, ig, ib, cn);
 							}
 						}
 						/* lanes whose walk ended are retired at the top of the loop */
@@ -659,7 +653,7 @@ __global__ void trace_shadow_kernel(DScene sc, const float *rays, const float *d
 	Counters cn = {};
 	const Ray r = { rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5], rays[6 * i], rays[6 * i + 1], rays[6 * i + 2] };
 	float lr = light[3 * i], lg = light[3 * i + 1], lb = light[3 * i + 2];
-	const bool b = trace_shadow<false>(sc, r, dist[i], emitter ? emitter[i] : -1, lr, lg, lb, cn);
+	const bool b = trace_shadow_wide<false>(sc, r, dist[i], emitter ? emitter[i] : -1, lr, lg, lb, cn);
 	light[3 * i] = lr;
 	light[3 * i + 1] = lg;
 	light[3 * i + 2] = lb;

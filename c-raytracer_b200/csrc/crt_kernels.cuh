@@ -14,12 +14,19 @@ constexpr int kChunkTiles = CRT_SHARD_CHUNK_TILES;            /* sharding granul
 constexpr int kWarpsPerBlock = 8;
 constexpr int kBlockThreads = kWarpsPerBlock * 32;
 #ifndef CRT_INNER_PER_VOTE
-#define CRT_INNER_PER_VOTE 4
+#define CRT_INNER_PER_VOTE 3
 #endif
 #ifndef CRT_PRIM_PER_VOTE
-#define CRT_PRIM_PER_VOTE 2
+#define CRT_PRIM_PER_VOTE 3
+#endif
+#ifndef CRT_INNER_WEIGHT
+#define CRT_INNER_WEIGHT 1
+#endif
+#ifndef CRT_PRIM_WEIGHT
+#define CRT_PRIM_WEIGHT 1
 #endif
 constexpr int kInnerPerVote = CRT_INNER_PER_VOTE, kPrimPerVote = CRT_PRIM_PER_VOTE; /* unit steps per warp vote */
+constexpr int kInnerWeight = CRT_INNER_WEIGHT, kPrimWeight = CRT_PRIM_WEIGHT;       /* node step iff ready_inner * Wi >= ready_prim * Wp */
 constexpr int kNumCounters = 11;
 #ifndef CRT_MIN_BLOCKS
 #define CRT_MIN_BLOCKS 2                   /* resident render blocks per SM the register budget is set for */
