@@ -14,7 +14,7 @@ options, seed) -- it is taken once, before timing, from the instrumented kernel
 instance, and is identical to the reference's own count (tests/test_gpu_parity).
 
 N > 1 (torchrun, one process per GPU): the scene is replicated, the frame is
-cut into 8x4-pixel tiles handed out in chunks of 8 tiles round-robin to the
+cut into 8x4-pixel tiles dealt round-robin to the
 ranks (crt_render_opts.shard_*), and the framebuffer is assembled on rank 0
 with one NCCL reduce(sum) of the disjoint, zero-elsewhere shards over NVLink.
 Total work is fixed, so scaling is "strong".
@@ -186,8 +186,7 @@ def ours(a):
         raise RuntimeError("bench.py: no CUDA device -- the trace loop has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner out of stdout: one JSON line only
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's banner must not share stdout with the JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -273,6 +272,15 @@ def ours(a):
         dist.all_reduce(elapsed, op=dist.ReduceOp.MAX)
     total_ms, kernel_avg_ms = float(elapsed[0]), float(elapsed[1])
     assemble_ms = ev_a0.elapsed_time(ev_a1) if world > 1 else 0.0  # last frame's assembly, incl. waiting for the slowest rank
+    assemble_alone_ms = 0.0
+    if world > 1:  # the collective by itself, ranks aligned (untimed by the headline)
+        barrier()
+        ev_a0.record()
+        for _ in range(5):
+            multigpu.assemble(d_raster, d_z, 0)
+        ev_a1.record()
+        torch.cuda.synchronize()
+        assemble_alone_ms = ev_a0.elapsed_time(ev_a1) / 5.0
     ms_per_step = total_ms / a.steps
     value = total_rays / (ms_per_step * 1e-3) / 1e6
 
@@ -334,7 +342,7 @@ def ours(a):
             "rays_per_frame": total_rays, "rays_closest": tot.rays_closest, "rays_shadow": tot.rays_shadow,
             "l2": "flushed between steps (256 MiB memset)", "parallelism": f"tile-chunk round-robin x{world}, scene replicated",
             "bvh_nodes": info.num_nodes, "bvh_build_ms": info.build_ms, "scene_upload_ms": info.upload_ms,
-            "scene_setup_s": setup_s, "seed": 1, "assemble_ms": assemble_ms,
+            "scene_setup_s": setup_s, "seed": 1, "assemble_ms": assemble_ms, "assemble_alone_ms": assemble_alone_ms,
         },
         "ms_per_frame": ms_per_step,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_frame": float(e2e_ms[0]),

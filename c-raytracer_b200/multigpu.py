@@ -3,9 +3,9 @@
 The reference parallelises render() over image rows with OpenMP (reference
 src/raytracer/render.c:349-352); pixels are independent and the scene is
 read-only.  Here the scene is replicated on every GPU and the frame is cut by
-the partition of include/crt.h (8x4-pixel tiles, chunks of 8 tiles dealt
-round-robin to the ranks, `crt_render_opts.shard_index / shard_count`): the
-interleave is fine enough (256 pixels) to even out the >10x cost differences
+the partition of include/crt.h (8x4-pixel tiles dealt round-robin to the
+ranks, `crt_render_opts.shard_index / shard_count`): the interleave is fine
+enough (32 pixels) to even out the >10x cost differences
 between sky, floor and glass.  Every rank renders its chunks into a zeroed
 full-size frame; the only exchange is the assembly of the disjoint shards on
 rank 0 -- one reduce(sum) over NVLink (NCCL) per buffer, 16 B per pixel.
@@ -27,7 +27,7 @@ def shard_options(opts, rank, world):
     return opts
 
 
-def shard_of_pixels(width, height, world, tile_w=8, tile_h=4, chunk_tiles=8):
+def shard_of_pixels(width, height, world, tile_w=8, tile_h=4, chunk_tiles=1):
     """(H, W) int tensor: owning shard of every pixel (the partition of include/crt.h)."""
     tiles_x = (width + tile_w - 1) // tile_w
     ys = torch.arange(height).unsqueeze(1)

@@ -151,7 +151,7 @@ enum crt_attenuation { CRT_ATTEN_NONE = 0, CRT_ATTEN_LINEAR = 1, CRT_ATTEN_SQUAR
  * chunk; chunk k belongs to shard k % shard_count. */
 #define CRT_TILE_W 8
 #define CRT_TILE_H 4
-#define CRT_SHARD_CHUNK_TILES 8
+#define CRT_SHARD_CHUNK_TILES 1
 
 /*
  * Per-frame parameters: the image plane `struct Image` (image.h:17-26, set up

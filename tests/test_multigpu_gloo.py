@@ -43,8 +43,8 @@ def test_partition_is_a_partition():
         owner = multigpu.shard_of_pixels(1920, 1080, world)
         counts = torch.bincount(owner.flatten(), minlength=world)
         assert int(counts.sum()) == 1920 * 1080
-        # round-robin chunks: shard sizes differ by at most a few chunks of 8 tiles x 32 pixels
-        assert int(counts.max() - counts.min()) <= 4 * 256
+        # round-robin tiles: shard sizes differ by at most a few tiles of 32 pixels
+        assert int(counts.max() - counts.min()) <= 8 * 32
     with pytest.raises(ValueError):
         from c_raytracer_b200 import _abi
         multigpu.shard_options(_abi.RenderOpts(), 2, 2)
