@@ -164,6 +164,45 @@ def test_ray_batches_match_oracle_large(gpu, scene):
     np.testing.assert_allclose(gl[free], ol[free], rtol=1e-6)
 
 
+@pytest.mark.parametrize("scene", ["scene4", "scene5_small", "scene6_small"])
+def test_shadow_rays_grazing_edges_match_oracle(gpu, scene):
+    """Shadow rays aimed exactly at triangle vertices and edges, with the light
+    distance set within a few ulp of the hit distance: every comparison of the
+    triangle test (u, v, u + v, t > epsilon, t < distance) sits on its threshold,
+    where the walk's division-free pre-test must hand over to the exact test."""
+    sc, dev = dev_scene(scene)
+    orc = oracle.OracleScene(sc)
+    rng = np.random.default_rng(11)
+    n = 200_000
+    tri = sc.objects[sc.objects["type"] == 1]
+    pick = tri[rng.integers(0, len(tri), n)]
+    kind = rng.integers(0, 4, n)
+    u = rng.uniform(0, 1, n).astype(np.float32)
+    bu = np.select([kind == 0, kind == 1, kind == 2, kind == 3], [u, np.zeros_like(u), u, np.round(u)])
+    bv = np.select([kind == 0, kind == 1, kind == 2, kind == 3], [np.zeros_like(u), u, 1 - u, np.round(1 - u) * (1 - np.round(u))])
+    tgt = (pick["a"] + bu[:, None] * pick["b"] + bv[:, None] * pick["c"]).astype(np.float32)
+    away = rng.normal(size=(n, 3)).astype(np.float32)
+    away /= np.linalg.norm(away, axis=1, keepdims=True)
+    org = (tgt + away * rng.uniform(0.01, 3, (n, 1))).astype(np.float32)
+    d = (tgt - org).astype(np.float32)
+    length = np.linalg.norm(d, axis=1).astype(np.float32)
+    d /= length[:, None]
+    rays = np.concatenate([d, org], 1).astype(np.float32)
+    dist = length.copy()
+    for k in range(1, 4):
+        sel = rng.integers(0, 8, n)
+        dist = np.where(sel == 2 * k - 1, np.nextafter(dist, np.float32(np.inf)), dist)
+        dist = np.where(sel == 2 * k, np.nextafter(dist, np.float32(0)), dist)
+    em = np.full(n, -1, np.int32)
+    light = np.ones((n, 3), np.float32)
+    gb, gl = dev.trace_shadow(rays, dist, em, light)
+    ob, ol = orc.trace_shadow(rays, dist, em, light)
+    assert 0.02 < gb.mean() < 0.98
+    np.testing.assert_array_equal(gb, ob)
+    free = gb == 0
+    np.testing.assert_allclose(gl[free], ol[free], rtol=1e-6)
+
+
 def test_empty_batches(gpu):
     sc, dev = dev_scene("scene1")
     obj, t, normal = dev.trace_closest(np.zeros((0, 6), np.float32))
