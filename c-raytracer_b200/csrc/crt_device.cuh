@@ -447,6 +447,36 @@ __device__ __forceinline__ bool shadow_can_prim(const ShadowWalk &w)
 	return w.leaf_left > 0 || w.qcount > 0;
 }
 
+/* The per-ray leaf queue, kLeafQueue entries.  In the render kernel it lives in
+ * shared memory as [slot][lane]; the lane's base is kept as a 32-bit shared
+ * address in a register the compiler cannot rematerialise (re-deriving it from
+ * %tid at every push cost 15 instructions, a fifth of the node step).  The
+ * one-ray-per-thread seam kernel uses a private array. */
+struct SharedLeafQueue {
+	uint32_t base; /* shared-space byte address of slot 0 of this lane */
+	__device__ __forceinline__ explicit SharedLeafQueue(const int *lane_slot0)
+	{
+		uint32_t b = static_cast<uint32_t>(__cvta_generic_to_shared(lane_slot0));
+		asm volatile("mov.u32 %0, %1;" : "=r"(base) : "r"(b));
+	}
+	__device__ __forceinline__ void put(int slot, int v) const
+	{
+		asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + (uint32_t)slot * 128u), "r"(v) : "memory");
+	}
+	__device__ __forceinline__ int get(int slot) const
+	{
+		int v;
+		asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + (uint32_t)slot * 128u) : "memory");
+		return v;
+	}
+};
+
+struct PrivateLeafQueue {
+	int *slots;
+	__device__ __forceinline__ void put(int slot, int v) const { slots[slot] = v; }
+	__device__ __forceinline__ int get(int slot) const { return slots[slot]; }
+};
+
 /* 1/d with a floor on |d|: keeps the quantised slab arithmetic finite (no 0 * inf) and
  * still puts both planes of an axis at -+huge for an axis-parallel ray */
 __device__ __forceinline__ float safe_rcp(float d)
@@ -459,18 +489,20 @@ struct RayWide {
 	float idx, idy, idz;
 };
 
-/* float(byte k of word) without a conversion instruction: place the byte in the mantissa of 2^23 */
+/* 2^23 + byte k of word, without a conversion instruction: the byte goes into the mantissa of 2^23 */
 __device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t selector)
 {
-	return __uint_as_float(__byte_perm(word, 0x4b000000u, selector)) - 8388608.f;
+	return __uint_as_float(__byte_perm(word, 0x4b000000u, selector));
 }
 
+constexpr float kSlabUlps = 9.5367431640625e-7f; /* 16 * 2^-24 */
+
 /* One visit of a quantised 8-wide node (bvh_build.h QuantNode): six vector loads,
- * eight slab tests.  qstride: 32 for the render kernel's [slot][lane] queue, 1 for a
- * private array. */
-template <bool COUNT, int QSTRIDE>
+ * eight slab tests; the child pushes are predicated, not branched (lanes hit
+ * different children). */
+template <bool COUNT, class QUEUE>
 __device__ __forceinline__ void shadow_inner_step(const DScene &sc, const Ray &r, const RayWide &rw, float dist, ShadowWalk &w,
-	int *stack, int *q, Counters &cn)
+	int *stack, const QUEUE &q, Counters &cn)
 {
 	const float4 *n = sc.wide + 6 * (size_t)w.node;
 	const float4 w0 = ldg4(n), w1 = ldg4(n + 1), w2 = ldg4(n + 2), w3 = ldg4(n + 3), w4 = ldg4(n + 4), w5 = ldg4(n + 5);
@@ -479,6 +511,22 @@ __device__ __forceinline__ void shadow_inner_step(const DScene &sc, const Ray &r
 	const float adjy = __uint_as_float(((eb >> 8) & 0xffu) << 23) * rw.idy;
 	const float adjz = __uint_as_float(((eb >> 16) & 0xffu) << 23) * rw.idz;
 	const float orgx = (w0.x - r.ox) * rw.idx, orgy = (w0.y - r.oy) * rw.idy, orgz = (w0.z - r.oz) * rw.idz;
+	/* The walk must never skip a child whose primitive the exact test would accept
+	 * (rays through shared edges and vertices, occluders within an ulp of the light
+	 * distance).  The plane distances q * adj + org carry a rounding error of at most
+	 * 6 ulp of (255 |adj| + |org|) against the true crossing (reciprocal, the two
+	 * products, the sums), so the near planes are pulled in and the far planes
+	 * pushed out by 16 ulp of (256 |adj| + |org|), per node and axis. */
+	const float ex = fmaf(fabsf(adjx), 256.f * kSlabUlps, fabsf(orgx) * kSlabUlps);
+	const float ey = fmaf(fabsf(adjy), 256.f * kSlabUlps, fabsf(orgy) * kSlabUlps);
+	const float ez = fmaf(fabsf(adjz), 256.f * kSlabUlps, fabsf(orgz) * kSlabUlps);
+	/* byte -> float costs one PRMT (2^23 + q in the mantissa); the 2^23 is taken
+	 * off in the constant term instead of per plane.  That term then has the
+	 * granularity of one quantisation step (ulp of 2^23 |adj|), so it is rounded
+	 * towards the outside of the slab. */
+	const float onx = __fmaf_rd(-8388608.f, adjx, orgx - ex), ofx = __fmaf_ru(-8388608.f, adjx, orgx + ex);
+	const float ony = __fmaf_rd(-8388608.f, adjy, orgy - ey), ofy = __fmaf_ru(-8388608.f, adjy, orgy + ey);
+	const float onz = __fmaf_rd(-8388608.f, adjz, orgz - ez), ofz = __fmaf_ru(-8388608.f, adjz, orgz + ez);
 	/* near / far planes by the sign of the direction */
 	const bool nx = rw.idx < 0.f, ny = rw.idy < 0.f, nz = rw.idz < 0.f;
 	const uint32_t nearx[2] = { __float_as_uint(nx ? w1.z : w1.x), __float_as_uint(nx ? w1.w : w1.y) };
@@ -492,37 +540,37 @@ __device__ __forceinline__ void shadow_inner_step(const DScene &sc, const Ray &r
 #pragma unroll
 	for (int i = 0; i < 8; i++) {
 		const uint32_t sel = 0x7540u + (uint32_t)(i & 3); /* bytes: (b_i, 0x00, 0x00, 0x4b) */
-		const float tnx = fmaf(byte_to_float(nearx[i >> 2], sel), adjx, orgx);
-		const float tny = fmaf(byte_to_float(neary[i >> 2], sel), adjy, orgy);
-		const float tnz = fmaf(byte_to_float(nearz[i >> 2], sel), adjz, orgz);
-		const float tfx = fmaf(byte_to_float(farx[i >> 2], sel), adjx, orgx);
-		const float tfy = fmaf(byte_to_float(fary[i >> 2], sel), adjy, orgy);
-		const float tfz = fmaf(byte_to_float(farz[i >> 2], sel), adjz, orgz);
+		const float tnx = fmaf(byte_to_float(nearx[i >> 2], sel), adjx, onx);
+		const float tny = fmaf(byte_to_float(neary[i >> 2], sel), adjy, ony);
+		const float tnz = fmaf(byte_to_float(nearz[i >> 2], sel), adjz, onz);
+		const float tfx = fmaf(byte_to_float(farx[i >> 2], sel), adjx, ofx);
+		const float tfy = fmaf(byte_to_float(fary[i >> 2], sel), adjy, ofy);
+		const float tfz = fmaf(byte_to_float(farz[i >> 2], sel), adjz, ofz);
 		const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
 		const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, dist));
 		if (code[i] != kStackSentinel)
 			Cnt<COUNT>::add(cn.box);
 		/* an empty child has near 255 / far 0 planes on every axis (and the sentinel code) */
-		if (tmin <= tmax && code[i] != kStackSentinel) {
-			if (code[i] >= 0) {
-				stack[w.sp++] = w.top;
-				w.top = code[i];
-			} else {
-				q[((w.qhead + w.qcount) & (kLeafQueue - 1)) * QSTRIDE] = code[i];
-				w.qcount++;
-			}
-		}
+		const bool hit = tmin <= tmax && code[i] != kStackSentinel;
+		const bool to_stack = hit && code[i] >= 0, to_queue = hit && code[i] < 0;
+		if (to_stack)
+			stack[w.sp] = w.top;
+		if (to_queue)
+			q.put((w.qhead + w.qcount) & (kLeafQueue - 1), code[i]);
+		w.sp += to_stack ? 1 : 0;
+		w.top = to_stack ? code[i] : w.top;
+		w.qcount += to_queue ? 1 : 0;
 	}
 	w.node = w.top;
 	w.top = w.sp > 0 ? stack[--w.sp] : kStackSentinel;
 }
 
-template <bool COUNT, int QSTRIDE>
+template <bool COUNT, class QUEUE>
 __device__ __forceinline__ void shadow_prim_step(const DScene &sc, const Ray &r, float dist, int emitter_object, ShadowWalk &w,
-	int *q, bool &blocked, float &lr, float &lg, float &lb, Counters &cn)
+	const QUEUE &q, bool &blocked, float &lr, float &lg, float &lb, Counters &cn)
 {
 	if (w.leaf_left == 0) {
-		const int leaf = ~q[w.qhead * QSTRIDE];
+		const int leaf = ~q.get(w.qhead);
 		w.qhead = (w.qhead + 1) & (kLeafQueue - 1);
 		w.qcount--;
 		w.leaf_first = leaf >> kLeafBits;
@@ -558,7 +606,8 @@ __device__ __forceinline__ bool trace_shadow_wide(const DScene &sc, const Ray &r
 	if (sc.num_nodes == 0)
 		return false;
 	int stack[kStackSize];
-	int q[kLeafQueue];
+	int slots[kLeafQueue];
+	const PrivateLeafQueue q = { slots };
 	ShadowWalk w;
 	shadow_walk_reset(w);
 	w.node = 0;
@@ -566,9 +615,9 @@ __device__ __forceinline__ bool trace_shadow_wide(const DScene &sc, const Ray &r
 	bool blocked = false;
 	while (shadow_walk_busy(w)) {
 		if (shadow_can_inner(w))
-			shadow_inner_step<COUNT, 1>(sc, r, rw, dist, w, stack, q, cn);
+			shadow_inner_step<COUNT>(sc, r, rw, dist, w, stack, q, cn);
 		else
-			shadow_prim_step<COUNT, 1>(sc, r, dist, emitter_object, w, q, blocked, lr, lg, lb, cn);
+			shadow_prim_step<COUNT>(sc, r, dist, emitter_object, w, q, blocked, lr, lg, lb, cn);
 	}
 	return blocked;
 }

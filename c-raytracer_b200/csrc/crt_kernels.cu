@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 					bool blocked = false;
 					ShadowWalk sw;
 					shadow_walk_reset(sw);
-					int *q = wqueue + warp_local * (kLeafQueue * 32) + lane;
+					const SharedLeafQueue q(wqueue + warp_local * (kLeafQueue * 32) + lane);
 					for (;;) {
 						/* -- service: finished lanes shade and store, idle lanes fetch -- */
 						const bool walking = have && shadow_walk_busy(sw);
@@ -460,12 +460,12 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 #pragma unroll 1
 								for (int k = 0; k < kInnerPerVote; k++)
 									if (have && shadow_can_inner(sw))
-										shadow_inner_step<COUNT, 32>(sc, sr, rw, dist, sw, stack, q, cn);
+										shadow_inner_step<COUNT>(sc, sr, rw, dist, sw, stack, q, cn);
 							} else {
 #pragma unroll 1
 								for (int k = 0; k < kPrimPerVote; k++)
 									if (have && shadow_can_prim(sw))
-										shadow_prim_step<COUNT, 32>(sc, sr, dist, em_object, sw, q, blocked, ir, ig, ib, cn);
+										shadow_prim_step<COUNT>(sc, sr, dist, em_object, sw, q, blocked, ir, ig, ib, cn);
 							}
 						}
 						/* lanes whose walk ended are retired at the top of the loop */

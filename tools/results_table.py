@@ -30,8 +30,8 @@ from oracle import oracle  # noqa: E402  (checker and CPU baseline only)
 
 # (scene, width, height, flags, (cpu_w, cpu_h) of the reference run)
 CONFIGS = [
-    ("scene1", 1920, 1080, [], (1920, 1080)),
-    ("scene3", 1920, 1080, [], (1920, 1080)),
+    ("scene1", 1920, 1080, [], (960, 540)),
+    ("scene3", 1920, 1080, [], (960, 540)),
     ("scene4", 1920, 1080, [], (480, 270)),
     ("scene5", 1920, 1080, ["-g", "path", "-n", "16"], (96, 54)),
     ("scene6", 3840, 2160, ["-g", "path", "-n", "2"], (192, 108)),
