@@ -118,14 +118,27 @@ __device__ __forceinline__ bool hit_triangle(const float4 p0, const float4 p1, c
 	const float hx = xsub(xmul(r.dy, p2.z), xmul(r.dz, p2.y));
 	const float hy = xsub(xmul(r.dz, p2.x), xmul(r.dx, p2.z));
 	const float hz = xsub(xmul(r.dx, p2.y), xmul(r.dy, p2.x));
-	const float a = xdot(p1.x, p1.y, p1.z, hx, hy, hz);
+	float a = xdot(p1.x, p1.y, p1.z, hx, hy, hz);
+	asm volatile("" : "+f"(a)); /* pin a: it was recomputed for the division */
 	if (a < eps && a > -eps) {
 		Cnt<COUNT>::add(cn.tri0);
 		return false;
 	}
-	const float f = __fdiv_rn(1.f, a);
 	const float sx = xsub(r.ox, p0.x), sy = xsub(r.oy, p0.y), sz = xsub(r.oz, p0.z);
-	const float u = xmul(f, xdot(sx, sy, sz, hx, hy, hz));
+	const float du = xdot(sx, sy, sz, hx, hy, hz);
+	/* u = fl(fl(1 / a) * du).  Over half of all tests end at u < 0 or u > 1, most of
+	 * them far from the thresholds, where the outcome follows from du and a
+	 * without the (16-instruction, exactly rounded) division: opposite signs give
+	 * u < 0 (the bounds keep the product from underflowing to -0, which would
+	 * pass), and |du| > |a| (1 + 8 ulp) gives u > 1 whatever the two roundings do. */
+	const float dus = a < 0.f ? -du : du, aa = fabsf(a);
+	if ((dus < -1e-28f && aa < 1e8f) || dus > aa * 1.000001f) {
+		Cnt<COUNT>::add(cn.tri1);
+		return false;
+	}
+	const float f = __fdiv_rn(1.f, a);
+	float u = xmul(f, du);
+	asm volatile("" : "+f"(u)); /* pin u: under register pressure it was recomputed (h, s.h, the product) for u + v */
 	if (u < 0.f || u > 1.f) {
 		Cnt<COUNT>::add(cn.tri1);
 		return false;
