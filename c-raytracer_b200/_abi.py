@@ -19,6 +19,9 @@ CRT_RENDER_COUNT_STATS = 1
 CRT_FUNC_SIN, CRT_FUNC_SAW, CRT_FUNC_TRIANGLE, CRT_FUNC_SQUARE = 0, 1, 2, 3
 CRT_OK, CRT_ERR_INVALID, CRT_ERR_NO_DEVICE, CRT_ERR_CUDA, CRT_ERR_NOMEM, CRT_ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5
 
+CRT_POST_BRIGHTEN, CRT_POST_DOF, CRT_POST_DOF_CAMERA, CRT_POST_MIST = 1, 2, 4, 8
+CRT_FALLOFF_QUADRATIC, CRT_FALLOFF_LINEAR, CRT_FALLOFF_INV_QUADRATIC = 0, 1, 2
+
 f3 = C.c_float * 3
 
 
@@ -84,6 +87,24 @@ class SceneInfo(C.Structure):
         ("total_lights", C.c_uint32), ("num_nodes", C.c_uint32), ("max_depth", C.c_uint32),
         ("device", C.c_uint32), ("sm_count", C.c_uint32),
         ("build_ms", C.c_double), ("upload_ms", C.c_double), ("device_bytes", C.c_uint64),
+    ]
+
+
+class PostOpts(C.Structure):
+    _fields_ = [
+        ("ops", C.c_uint32), ("brighten", C.c_float),
+        ("dof_scale", C.c_float), ("dof_bias", C.c_float),
+        ("dof_aperture", C.c_float), ("dof_focal_length", C.c_float), ("dof_plane_in_focus", C.c_float),
+        ("mist_start", C.c_float), ("mist_depth", C.c_float), ("mist_falloff", C.c_uint32), ("mist_color", f3),
+        ("reserved", C.c_uint32 * 3),
+    ]
+
+
+class PostStats(C.Structure):
+    _fields_ = [
+        ("kernel_ms", C.c_double), ("total_ms", C.c_double),
+        ("dof_scale", C.c_float), ("dof_bias", C.c_float),
+        ("dof_max_radius", C.c_uint32), ("launches", C.c_uint32),
     ]
 
 

@@ -52,6 +52,15 @@ float as_float(uint32_t u)
 
 } // namespace
 
+int crt::api_fail(int code, const char *fmt, ...)
+{
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_error, sizeof g_error, fmt, ap);
+	va_end(ap);
+	return code;
+}
+
 struct crt_scene {
 	int device = 0;
 	int sm_count = 0;
@@ -136,6 +145,11 @@ int ensure_device(int device)
 }
 
 } // namespace
+
+int crt::api_ensure_device(int device)
+{
+	return ensure_device(device);
+}
 
 extern "C" {
 

@@ -65,6 +65,12 @@ void launch_texture_eval(const DScene &sc, int32_t material, const float *points
 /* returns FLOPs executed per launch */
 double launch_fma_peak(int blocks, int threads, int iters, float *sink, cudaStream_t stream);
 
+/* shared by the API translation units (crt_api.cu, crt_post.cu): sets
+ * crt_last_error() and returns `code`; selects the device or fails with
+ * CRT_ERR_NO_DEVICE / CRT_ERR_INVALID */
+int api_fail(int code, const char *fmt, ...);
+int api_ensure_device(int device);
+
 } // namespace crt
 
 #endif

@@ -19,6 +19,7 @@ SYMBOLS = [
     "crt_scene_create", "crt_scene_destroy", "crt_scene_get_info",
     "crt_render", "crt_render_device", "crt_render_device_sync",
     "crt_trace_closest", "crt_trace_shadow", "crt_texture_eval", "crt_measure_fp32_peak",
+    "crt_postprocess", "crt_postprocess_device",
 ]
 
 _lib = None
@@ -47,6 +48,9 @@ def lib():
         L.crt_trace_shadow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         L.crt_texture_eval.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_size_t, C.c_void_p]
         L.crt_measure_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
+        L.crt_postprocess.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.crt_postprocess_device.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -64,6 +68,25 @@ def measure_fp32_peak(device=0):
     v = C.c_double()
     _check(lib().crt_measure_fp32_peak(device, C.byref(v)))
     return v.value
+
+
+def postprocess(opts, raster, z_buffer, device=0, stats=None):
+    """crt_postprocess: brighten / depth of field / mist on a host frame (H, W, 3) + (H, W);
+    returns the processed raster (a new array)."""
+    z = np.ascontiguousarray(z_buffer, dtype=np.float32)
+    out = np.array(raster, dtype=np.float32, order="C", copy=True)
+    h, w = z.shape
+    assert out.shape == (h, w, 3)
+    _check(lib().crt_postprocess(device, C.addressof(opts), w, h, out.ctypes.data, z.ctypes.data,
+                                 C.addressof(stats) if stats is not None else None))
+    return out
+
+
+def postprocess_device(opts, width, height, d_raster_ptr, d_z_ptr, device=0, stream=None, stats=None):
+    """crt_postprocess_device: in place on device pointers (e.g. the buffers crt_render_device filled)."""
+    _check(lib().crt_postprocess_device(device, C.addressof(opts), width, height, C.c_void_p(d_raster_ptr), C.c_void_p(d_z_ptr),
+                                        C.c_void_p(stream) if stream else None,
+                                        C.addressof(stats) if stats is not None else None))
 
 
 class DeviceScene:

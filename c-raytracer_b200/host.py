@@ -29,6 +29,11 @@ def lib():
         L.rt_host_save.argtypes = [C.c_char_p, C.c_uint, C.c_uint, C.c_void_p, C.c_void_p, C.c_int]
         L.rt_host_save.restype = C.c_int
         L.rt_host_quantize.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+        L.rt_host_post_opts_parse.argtypes = [C.POINTER(_abi.PostOpts), C.c_int, C.POINTER(C.c_char_p)]
+        L.rt_host_load_raw.argtypes = [C.c_char_p, C.POINTER(C.c_uint), C.POINTER(C.c_uint),
+                                       C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.POINTER(C.c_float))]
+        L.rt_host_free.argtypes = [C.c_void_p]
+        L.rt_host_free.restype = None
         _lib = L
     return _lib
 
@@ -86,6 +91,34 @@ class Scene:
             arr = (C.c_char_p * len(argv))(*argv)
             lib().rt_host_opts_parse(C.byref(o), len(argv), arr)
         return o
+
+
+def post_options(*flags):
+    """The post-processor's command-line flags as a PostOpts, e.g.
+    post_options("-b", 1.5, "--dof", 2, -4, "--mist", 3, 10, "lin", .5, .5, .6)
+    (reference src/postprocess/postproc.c:36-92)."""
+    o = _abi.PostOpts()
+    argv = [b"postprocess"] + [str(f).encode() for f in flags]
+    arr = (C.c_char_p * len(argv))(*argv)
+    if lib().rt_host_post_opts_parse(C.byref(o), len(argv), arr):
+        raise SceneError(lib().rt_host_last_error().decode())
+    return o
+
+
+def load_raw(path):
+    """(raster (H, W, 3), z_buffer (H, W)) of a raw frame (-f): what the post-processor reads
+    (reference src/postprocess/image.c:30-73)."""
+    w, h = C.c_uint(), C.c_uint()
+    pr, pz = C.POINTER(C.c_float)(), C.POINTER(C.c_float)()
+    if lib().rt_host_load_raw(os.fsencode(path), C.byref(w), C.byref(h), C.byref(pr), C.byref(pz)):
+        raise SceneError(lib().rt_host_last_error().decode())
+    try:
+        raster = np.ctypeslib.as_array(pr, shape=(h.value, w.value, 3)).copy()
+        z = np.ctypeslib.as_array(pz, shape=(h.value, w.value)).copy()
+    finally:
+        lib().rt_host_free(pr)
+        lib().rt_host_free(pz)
+    return raster, z
 
 
 def quantize(raster):

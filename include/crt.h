@@ -258,6 +258,53 @@ int crt_texture_eval(crt_scene *scene, int32_t material, const float *points,
  * denominator of the ray-test roofline. */
 int crt_measure_fp32_peak(int device, double *tflops);
 
+/* ---- post-processing of a rendered frame ------------------------
+ * Replaces postprocess() (reference src/postprocess/postproc.c:36-92) and the
+ * three operations behind it: brighten() :94-102, depth_of_field() :104-160,
+ * mist() :162-188.  They consume exactly what crt_render() produces (raster
+ * and z-buffer), in the reference's fixed order brighten -> depth of field ->
+ * mist, each applied when its bit is set in `ops`. */
+enum crt_post_op {
+	CRT_POST_BRIGHTEN = 1,   /* -b <factor> */
+	CRT_POST_DOF = 2,        /* --dof <scale> <bias> */
+	CRT_POST_DOF_CAMERA = 4, /* --dof-camera <aperture> <focal length> <plane in focus>; ignored when CRT_POST_DOF is set (postproc.c:47-52) */
+	CRT_POST_MIST = 8        /* --mist <start> <depth> <falloff> <r> <g> <b> */
+};
+
+enum crt_post_falloff { /* enum Falloff, postproc.c:26-30 */
+	CRT_FALLOFF_QUADRATIC = 0,
+	CRT_FALLOFF_LINEAR = 1,
+	CRT_FALLOFF_INV_QUADRATIC = 2
+};
+
+typedef struct crt_post_opts {
+	uint32_t ops; /* crt_post_op bits */
+	float brighten;
+	float dof_scale, dof_bias;
+	float dof_aperture, dof_focal_length, dof_plane_in_focus;
+	float mist_start, mist_depth;
+	uint32_t mist_falloff; /* crt_post_falloff */
+	float mist_color[3];
+	uint32_t reserved[3];
+} crt_post_opts;
+
+typedef struct crt_post_stats {
+	double kernel_ms;   /* all post-processing kernels, CUDA events */
+	double total_ms;    /* including copies (crt_postprocess only) */
+	float dof_scale, dof_bias; /* the values depth_of_field() ran with (derived for --dof-camera) */
+	uint32_t dof_max_radius;   /* largest circle-of-confusion radius in pixels */
+	uint32_t launches;         /* kernels launched */
+} crt_post_stats;
+
+/* raster = W*H*3 floats in/out, z_buffer = W*H floats in; HOST memory. */
+int crt_postprocess(int device, const crt_post_opts *opts, uint32_t width, uint32_t height,
+	float *raster, const float *z_buffer, crt_post_stats *stats);
+/* Same on DEVICE pointers of `device` (the buffers crt_render_device() filled),
+ * enqueued on `cuda_stream`; synchronises before returning only when stats is
+ * not NULL or CRT_POST_DOF_CAMERA needs the z range on the host. */
+int crt_postprocess_device(int device, const crt_post_opts *opts, uint32_t width, uint32_t height,
+	float *d_raster, const float *d_z_buffer, void *cuda_stream, crt_post_stats *stats);
+
 #ifdef __cplusplus
 }
 #endif

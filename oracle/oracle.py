@@ -15,6 +15,8 @@ ORACLE_SO = os.path.join(HERE, "liboracle.so")
 REF_ENGINE = os.path.join(HERE, "_ref", "ref_engine")
 ENGINE_REF = os.path.join(HERE, "_ref", "engine_ref")
 ENGINE_REF_STOCK = os.path.join(HERE, "_ref", "engine_ref_stock")
+REF_POST = os.path.join(HERE, "_ref", "ref_post")                 # reference post-processor, FP32 raster dumped
+POSTPROCESS_REF = os.path.join(HERE, "_ref", "postprocess_ref")   # the reference's own postprocess executable
 
 _lib = None
 
@@ -35,6 +37,7 @@ def lib():
         L.oracle_simplex_noise.restype = C.c_float
         L.oracle_simplex_noise.argtypes = [C.c_float, C.c_float, C.c_float]
         L.oracle_primitive_hit.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.oracle_postprocess.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -96,6 +99,30 @@ def simplex_noise(points):
 
 
 # ---- the compiled reference (oracle/_ref) ---------------------------------
+
+def postprocess(opts, raster, z_buffer, stats=None):
+    """CPU restatement of the reference's postprocess() (crt_oracle_post.c); returns a new raster.
+    Raises ValueError with the crt status on rejected options."""
+    z = np.ascontiguousarray(z_buffer, dtype=np.float32)
+    out = np.array(raster, dtype=np.float32, order="C", copy=True)
+    h, w = z.shape
+    rc = lib().oracle_postprocess(C.addressof(opts), w, h, out.ctypes.data, z.ctypes.data,
+                                  C.addressof(stats) if stats is not None else None)
+    if rc:
+        raise ValueError(rc)
+    return out
+
+
+def ref_postprocess(raw_tiff, flags):
+    """FP32 raster left by the UNMODIFIED reference postprocess() (oracle/_ref/ref_post) run on
+    a raw TIFF with the reference's own flags."""
+    with tempfile.TemporaryDirectory() as d:
+        out = os.path.join(d, "out.f32")
+        _run([REF_POST, raw_tiff, out] + [str(f) for f in flags])
+        b = open(out, "rb").read()
+    w, h = (int(x) for x in np.frombuffer(b[:8], dtype=np.uint32))
+    return np.frombuffer(b[8:], dtype=np.float32).reshape(h, w, 3).copy()
+
 
 def have_ref():
     return os.path.exists(REF_ENGINE)

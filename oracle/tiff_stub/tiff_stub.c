@@ -2,7 +2,9 @@
  * tiff_stub.c -- TEST INFRASTRUCTURE (oracle).  Implements the handful of
  * libtiff calls the reference's raytracer/image.c:64-139 makes, writing an
  * uncompressed little-endian baseline TIFF with RowsPerStrip=1 and, when set,
- * the private tag 65000 (FLOAT array) carrying the z-buffer.
+ * the private tag 65000 (FLOAT array) carrying the z-buffer; and the calls of
+ * postprocess/image.c:30-73, reading such a file back (little-endian,
+ * uncompressed, any strip layout).
  */
 #include "tiffio.h"
 
@@ -17,10 +19,133 @@ struct tiff_stub {
 	uint32_t zcount;
 	const float *z;
 	uint8_t *rows;
+	/* read side */
+	int reading;
+	uint8_t *file;
+	size_t file_size;
+	uint32_t *strip_off, strips;
+	float *zread;
 };
+
+static uint32_t rd(const TIFF *t, size_t off, int bytes)
+{
+	uint32_t v = 0;
+	if (off + (size_t)bytes <= t->file_size)
+		memcpy(&v, t->file + off, (size_t)bytes);
+	return v;
+}
+
+static TIFF *open_read(const char *filename)
+{
+	FILE *f = fopen(filename, "rb");
+	if (!f)
+		return NULL;
+	TIFF *t = calloc(1, sizeof *t);
+	t->reading = 1;
+	fseek(f, 0, SEEK_END);
+	t->file_size = (size_t)ftell(f);
+	fseek(f, 0, SEEK_SET);
+	t->file = malloc(t->file_size ? t->file_size : 1);
+	if (fread(t->file, 1, t->file_size, f) != t->file_size || t->file_size < 8 || memcmp(t->file, "II*\0", 4)) {
+		fclose(f);
+		free(t->file);
+		free(t);
+		return NULL;
+	}
+	fclose(f);
+	t->rps = 0xffffffffu;
+	t->planar = 1;
+	t->spp = 1;
+	t->bps = 1;
+	const size_t ifd = rd(t, 4, 4);
+	const uint32_t n = rd(t, ifd, 2);
+	for (uint32_t k = 0; k < n; k++) {
+		const size_t e = ifd + 2 + 12 * (size_t)k;
+		const uint32_t tag = rd(t, e, 2), type = rd(t, e + 2, 2), count = rd(t, e + 4, 4);
+		const int size = type == 3 ? 2 : 4;
+		const size_t data = (size_t)count * size <= 4 ? e + 8 : rd(t, e + 8, 4);
+		const uint32_t first = rd(t, data, size);
+		switch (tag) {
+		case TIFFTAG_IMAGEWIDTH: t->width = first; break;
+		case TIFFTAG_IMAGELENGTH: t->height = first; break;
+		case TIFFTAG_BITSPERSAMPLE: t->bps = first; break;
+		case TIFFTAG_SAMPLESPERPIXEL: t->spp = first; break;
+		case TIFFTAG_PHOTOMETRIC: t->photometric = first; break;
+		case TIFFTAG_ORIENTATION: t->orientation = first; break;
+		case TIFFTAG_PLANARCONFIG: t->planar = first; break;
+		case TIFFTAG_ROWSPERSTRIP: t->rps = first; break;
+		case 273:
+			t->strips = count;
+			t->strip_off = malloc(sizeof(uint32_t) * (count ? count : 1));
+			for (uint32_t i = 0; i < count; i++)
+				t->strip_off[i] = rd(t, data + (size_t)i * size, size);
+			break;
+		case 65000:
+			t->zcount = count;
+			t->zread = malloc(sizeof(float) * (count ? count : 1));
+			if (data + 4 * (size_t)count <= t->file_size)
+				memcpy(t->zread, t->file + data, 4 * (size_t)count);
+			break;
+		default: break;
+		}
+	}
+	if (t->rps > t->height)
+		t->rps = t->height;
+	return t;
+}
+
+TIFFErrorHandler TIFFSetWarningHandler(TIFFErrorHandler handler)
+{
+	(void)handler;
+	return NULL;
+}
+
+/* the reference reads every scalar tag into a uint16_t (postprocess/image.c:41-46) */
+int TIFFGetField(TIFF *t, ttag_t tag, ...)
+{
+	va_list ap;
+	va_start(ap, tag);
+	int ok = 1;
+	switch (tag) {
+	case TIFFTAG_IMAGEWIDTH: *va_arg(ap, uint16_t *) = (uint16_t)t->width; break;
+	case TIFFTAG_IMAGELENGTH: *va_arg(ap, uint16_t *) = (uint16_t)t->height; break;
+	case TIFFTAG_BITSPERSAMPLE: *va_arg(ap, uint16_t *) = (uint16_t)t->bps; break;
+	case TIFFTAG_SAMPLESPERPIXEL: *va_arg(ap, uint16_t *) = (uint16_t)t->spp; break;
+	case TIFFTAG_PLANARCONFIG: *va_arg(ap, uint16_t *) = (uint16_t)t->planar; break;
+	case 65000: {
+		uint32_t *count = va_arg(ap, uint32_t *);
+		float **data = va_arg(ap, float **);
+		*count = t->zcount;
+		*data = t->zread;
+		ok = t->zread != NULL;
+		break;
+	}
+	default: ok = 0; break;
+	}
+	va_end(ap);
+	return ok;
+}
+
+tsize_t TIFFScanlineSize(TIFF *t) { return (tsize_t)t->width * t->spp * (t->bps / 8); }
+
+int TIFFReadScanline(TIFF *t, tdata_t buf, uint32_t row, uint16_t sample)
+{
+	(void)sample;
+	const size_t rb = (size_t)TIFFScanlineSize(t);
+	const uint32_t strip = row / t->rps;
+	if (strip >= t->strips)
+		return -1;
+	const size_t off = t->strip_off[strip] + rb * (row % t->rps);
+	if (off + rb > t->file_size)
+		return -1;
+	memcpy(buf, t->file + off, rb);
+	return 1;
+}
 
 TIFF *TIFFOpen(const char *filename, const char *mode)
 {
+	if (mode && mode[0] == 'r')
+		return open_read(filename);
 	if (!mode || mode[0] != 'w')
 		return NULL;
 	TIFF *t = calloc(1, sizeof *t);
@@ -84,6 +209,13 @@ static void put_entry(uint8_t **p, uint16_t tag, uint16_t type, uint32_t count, 
 
 void TIFFClose(TIFF *t)
 {
+	if (t->reading) {
+		free(t->file);
+		free(t->strip_off);
+		free(t->zread);
+		free(t);
+		return;
+	}
 	size_t rb = (size_t)t->width * t->spp * (t->bps / 8);
 	uint32_t n_entries = 11 + (t->z ? 1 : 0);
 	uint32_t off_ifd = 8;

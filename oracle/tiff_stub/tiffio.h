@@ -2,8 +2,9 @@
  * tiffio.h -- TEST INFRASTRUCTURE (oracle).  Minimal stand-in for libtiff's
  * header so that the unmodified reference src/raytracer/image.c (which
  * includes <tiffio.h>, image.c:25) compiles in a container without libtiff
- * (SURVEY F2).  Only the calls image.c:64-139 makes are provided; they are
- * implemented in tiff_stub.c and write a real baseline TIFF.
+ * (SURVEY F2).  Only the calls raytracer/image.c:64-139 (write side) and
+ * postprocess/image.c:30-73 (read side) make are provided; they are
+ * implemented in tiff_stub.c and write / read a real baseline TIFF.
  */
 #ifndef ORACLE_TIFFIO_STUB_H
 #define ORACLE_TIFFIO_STUB_H
@@ -51,6 +52,12 @@ int TIFFMergeFieldInfo(TIFF *tif, const TIFFFieldInfo info[], uint32_t n);
 tsize_t TIFFStripSize(TIFF *tif);
 tstrip_t TIFFNumberOfStrips(TIFF *tif);
 int TIFFWriteScanline(TIFF *tif, tdata_t buf, uint32_t row, uint16_t sample);
+/* read side */
+typedef void (*TIFFErrorHandler)(const char *, const char *, void *);
+TIFFErrorHandler TIFFSetWarningHandler(TIFFErrorHandler handler);
+int TIFFGetField(TIFF *tif, ttag_t tag, ...);
+tsize_t TIFFScanlineSize(TIFF *tif);
+int TIFFReadScanline(TIFF *tif, tdata_t buf, uint32_t row, uint16_t sample);
 void *_TIFFmalloc(tsize_t size);
 void _TIFFfree(void *ptr);
 

@@ -8,6 +8,8 @@
 #include "image.h"
 #include "render.h"
 #include "scene.h"
+#include "tiff.h"
+#include "../postprocess/options.h"
 
 static _Thread_local char last_error[RT_ERRLEN];
 
@@ -57,6 +59,41 @@ void rt_host_opts_parse(crt_render_opts *opts, int argc, char **argv)
 		return;
 	rt_render_parse(opts, &args);
 	rt_args_free(&args);
+}
+
+int rt_host_post_opts_parse(crt_post_opts *opts, int argc, char **argv)
+{
+	struct rt_args args;
+	if (rt_args_init(&args, argc, argv)) {
+		snprintf(last_error, sizeof last_error, "out of memory");
+		return -1;
+	}
+	const int rc = rt_post_options(&args, opts, last_error);
+	rt_args_free(&args);
+	return rc;
+}
+
+int rt_host_load_raw(const char *filename, unsigned *width, unsigned *height, float **raster, float **z_buffer)
+{
+	struct rt_tiff_image img;
+	if (rt_tiff_read(filename, &img, last_error))
+		return -1;
+	if (img.bits_per_sample != 32 || !img.raster || !img.z_buffer || img.z_count != (uint32_t)((size_t)img.width * img.height)) {
+		snprintf(last_error, sizeof last_error, "[%s] is not a raw frame (32 bits per sample with a z-buffer)", filename);
+		rt_tiff_free(&img);
+		return -1;
+	}
+	*width = img.width;
+	*height = img.height;
+	*raster = img.raster;
+	*z_buffer = img.z_buffer;
+	free(img.rgb8);
+	return 0;
+}
+
+void rt_host_free(void *p)
+{
+	free(p);
 }
 
 int rt_host_save(const char *filename, unsigned width, unsigned height, const float *raster, const float *z_buffer, int raw)

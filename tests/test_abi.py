@@ -16,14 +16,17 @@ def test_struct_sizes_match_c(tmp_path):
     src = tmp_path / "sizes.c"
     src.write_text(
         '#include <stdio.h>\n#include <stddef.h>\n#include "crt.h"\n'
-        'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(crt_material), sizeof(crt_object),'
+        'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(crt_material), sizeof(crt_object),'
         ' sizeof(crt_scene_desc), sizeof(crt_render_opts), sizeof(crt_stats), sizeof(crt_scene_info),'
-        ' offsetof(crt_render_opts, seed), offsetof(crt_stats, kernel_ms)); return 0;}\n')
+        ' offsetof(crt_render_opts, seed), offsetof(crt_stats, kernel_ms), sizeof(crt_post_opts), sizeof(crt_post_stats),'
+        ' offsetof(crt_post_opts, mist_color), offsetof(crt_post_stats, dof_max_radius)); return 0;}\n')
     exe = tmp_path / "sizes"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
     assert got == [C.sizeof(_abi.Material), C.sizeof(_abi.Object), C.sizeof(_abi.SceneDesc), C.sizeof(_abi.RenderOpts),
-                   C.sizeof(_abi.Stats), C.sizeof(_abi.SceneInfo), _abi.RenderOpts.seed.offset, _abi.Stats.kernel_ms.offset]
+                   C.sizeof(_abi.Stats), C.sizeof(_abi.SceneInfo), _abi.RenderOpts.seed.offset, _abi.Stats.kernel_ms.offset,
+                   C.sizeof(_abi.PostOpts), C.sizeof(_abi.PostStats), _abi.PostOpts.mist_color.offset,
+                   _abi.PostStats.dof_max_radius.offset]
     assert got[0] == 128 and got[1] == 64
 
 
