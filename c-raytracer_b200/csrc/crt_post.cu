@@ -21,6 +21,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <mutex>
 
 #include "crt_kernels.cuh"
 
@@ -181,8 +182,11 @@ __global__ void __launch_bounds__(kSeg *kRows) dof_prepare_kernel(const float *r
 		m = max(m, __shfl_xor_sync(0xffffffffu, m, d));
 	if (threadIdx.x == 0) {
 		seg_rmax[(size_t)y * p.nseg + blockIdx.x] = (uint16_t)m;
-		atomicMax(row_rmax + y, m);
-		atomicMax(frame_rmax, m);
+		/* test before the atomic: 65 k warps of a 1080p frame would otherwise serialise on one word */
+		if (m > *(volatile int *)(row_rmax + y))
+			atomicMax(row_rmax + y, m);
+		if (m > *(volatile int *)frame_rmax)
+			atomicMax(frame_rmax, m);
 	}
 }
 
@@ -209,11 +213,13 @@ __global__ void __launch_bounds__(kSeg *kRows) dof_gather_kernel(float *raster, 
 		for (int sg = sg0; sg <= sg1; sg++) {
 			const int s0 = sg * kSeg;
 			const int reach = max(dy, max(s0 - tx, tx - (s0 + kSeg - 1)));
-			if ((int)__ldg(seg_rmax + (size_t)sy * p.nseg + sg) < reach)
+			const int rm = __ldg(seg_rmax + (size_t)sy * p.nseg + sg);
+			if (rm < reach)
 				continue;
-			const int s1 = min(s0 + kSeg, (int)p.w);
+			/* no source of this segment reaches further than rm pixels */
+			const int x0 = max(s0, tx - rm), x1 = min(min(s0 + kSeg, (int)p.w), tx + rm + 1);
 			const size_t row = (size_t)sy * p.w;
-			for (int sx = s0; sx < s1; sx++) {
+			for (int sx = x0; sx < x1; sx++) {
 				const int r = __ldg(radius + row + sx), dx = abs(tx - sx);
 				if (dx > r || dy > r)
 					continue;
@@ -241,6 +247,45 @@ struct Scratch {
 	void *p = nullptr;
 	~Scratch() { cudaFree(p); }
 };
+
+/* Scratch of the depth-of-field kernels, kept per device between calls (a
+ * cudaMalloc / cudaFree pair per frame costs more than the kernels).  Calls
+ * that reuse it are ordered on the device by an event: the next call's stream
+ * waits for the previous call's last kernel. */
+struct Workspace {
+	void *p = nullptr;
+	size_t bytes = 0;
+	cudaEvent_t last_use = nullptr;
+};
+constexpr int kMaxDevices = 64;
+Workspace g_workspace[kMaxDevices];
+std::mutex g_workspace_mutex;
+
+int workspace_acquire(int device, size_t bytes, cudaStream_t stream, void **out)
+{
+	Workspace &w = g_workspace[device];
+	if (!w.last_use)
+		POST_TRY(cudaEventCreateWithFlags(&w.last_use, cudaEventDisableTiming));
+	if (w.bytes < bytes) {
+		if (w.p) {
+			POST_TRY(cudaEventSynchronize(w.last_use));
+			POST_TRY(cudaFree(w.p));
+			w.p = nullptr;
+			w.bytes = 0;
+		}
+		POST_TRY(cudaMalloc(&w.p, bytes));
+		w.bytes = bytes;
+	} else {
+		POST_TRY(cudaStreamWaitEvent(stream, w.last_use, 0));
+	}
+	*out = w.p;
+	return CRT_OK;
+}
+
+size_t align_up(size_t v)
+{
+	return (v + 255) & ~(size_t)255;
+}
 
 int run_pointwise(float *d_raster, const float *d_z, size_t pixels, const PointOps &o, cudaStream_t stream, uint32_t &launches)
 {
@@ -340,16 +385,26 @@ int crt_postprocess_device(int device, const crt_post_opts *opts, uint32_t width
 		p.bias = bias;
 		p.brighten = before.brighten;
 		p.factor = before.factor;
-		Scratch src, radius, seg, rows;
-		POST_TRY(cudaMalloc(&src.p, pixels * sizeof(float4)));
-		POST_TRY(cudaMalloc(&radius.p, pixels * sizeof(uint16_t)));
-		POST_TRY(cudaMalloc(&seg.p, (size_t)p.nseg * height * sizeof(uint16_t)));
-		POST_TRY(cudaMalloc(&rows.p, ((size_t)height + 1) * sizeof(int)));
-		POST_TRY(cudaMemsetAsync(rows.p, 0, ((size_t)height + 1) * sizeof(int), stream));
-		int *row_rmax = static_cast<int *>(rows.p), *frame_rmax = row_rmax + height;
+		if (device >= kMaxDevices)
+			return api_fail(CRT_ERR_UNSUPPORTED, "device ordinal %d", device);
+		std::lock_guard<std::mutex> lock(g_workspace_mutex);
+		const size_t src_bytes = align_up(pixels * sizeof(float4)), radius_bytes = align_up(pixels * sizeof(uint16_t));
+		const size_t seg_bytes = align_up((size_t)p.nseg * height * sizeof(uint16_t)), rows_bytes = align_up(((size_t)height + 1) * sizeof(int));
+		void *base = nullptr;
+		rc = workspace_acquire(device, src_bytes + radius_bytes + seg_bytes + rows_bytes, stream, &base);
+		if (rc)
+			return rc;
+		char *cursor = static_cast<char *>(base);
+		float4 *src = reinterpret_cast<float4 *>(cursor);
+		cursor += src_bytes;
+		uint16_t *radius = reinterpret_cast<uint16_t *>(cursor);
+		cursor += radius_bytes;
+		uint16_t *seg = reinterpret_cast<uint16_t *>(cursor);
+		cursor += seg_bytes;
+		int *row_rmax = reinterpret_cast<int *>(cursor), *frame_rmax = row_rmax + height;
+		POST_TRY(cudaMemsetAsync(row_rmax, 0, ((size_t)height + 1) * sizeof(int), stream));
 		const dim3 block(kSeg, kRows), grid(p.nseg, (height + kRows - 1) / kRows);
-		dof_prepare_kernel<<<grid, block, 0, stream>>>(d_raster, d_z, p, static_cast<float4 *>(src.p), static_cast<uint16_t *>(radius.p),
-			static_cast<uint16_t *>(seg.p), row_rmax, frame_rmax);
+		dof_prepare_kernel<<<grid, block, 0, stream>>>(d_raster, d_z, p, src, radius, seg, row_rmax, frame_rmax);
 		st.launches++;
 		int rmax = 0;
 		POST_TRY(cudaMemcpyAsync(&rmax, frame_rmax, sizeof rmax, cudaMemcpyDeviceToHost, stream));
@@ -358,11 +413,10 @@ int crt_postprocess_device(int device, const crt_post_opts *opts, uint32_t width
 			return api_fail(CRT_ERR_UNSUPPORTED, "depth of field: a circle of confusion of %d pixels or more (scale %g, bias %g)", kMaxRadius,
 				(double)scale, (double)bias);
 		st.dof_max_radius = (uint32_t)rmax;
-		dof_gather_kernel<<<grid, block, 0, stream>>>(d_raster, d_z, p, static_cast<const float4 *>(src.p),
-			static_cast<const uint16_t *>(radius.p), static_cast<const uint16_t *>(seg.p), row_rmax, frame_rmax, after);
+		dof_gather_kernel<<<grid, block, 0, stream>>>(d_raster, d_z, p, src, radius, seg, row_rmax, frame_rmax, after);
 		st.launches++;
 		POST_TRY(cudaGetLastError());
-		POST_TRY(cudaStreamSynchronize(stream)); /* the scratch buffers are freed on return */
+		POST_TRY(cudaEventRecord(g_workspace[device].last_use, stream));
 	}
 	if (stats) {
 		float ms = 0.f;

@@ -111,7 +111,7 @@ def test_full_size_properties(gpu, w, h):
 
 def test_full_hd_depth_of_field_equals_oracle(gpu):
     raster, z = seeded_frame(1920, 1080, 41)
-    o = host.post_options("--dof", 0.9, -5, "--mist", 5, 8, "lin", 0.6, 0.6, 0.7)
+    o = host.post_options("--dof", 1.6, -8, "--mist", 5, 8, "lin", 0.6, 0.6, 0.7)
     st = _abi.PostStats()
     got = device.postprocess(o, raster, z, gpu, st)
     assert st.dof_max_radius >= 4
