@@ -256,10 +256,13 @@ def ours(a):
     barrier()
     kernel_ms = []
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    step_marks = [torch.cuda.Event(enable_timing=True) for _ in range(a.steps + 1)]
     t_wall0 = time.time()
     ev0.record()
-    for _ in range(a.steps):
+    step_marks[0].record()
+    for k in range(a.steps):
         step_device()
+        step_marks[k + 1].record()
         kst = _abi.Stats()
         dev.sync(kst)  # per-frame kernel time from the library's own events on the launch stream
         kernel_ms.append(kst.kernel_ms)
@@ -271,6 +274,16 @@ def ours(a):
     if world > 1:
         dist.all_reduce(elapsed, op=dist.ReduceOp.MAX)
     total_ms, kernel_avg_ms = float(elapsed[0]), float(elapsed[1])
+    # per rank and step: the render kernel alone, and the whole step (flush + kernel + waiting for the other ranks + assembly)
+    torch.cuda.synchronize()
+    mine = torch.tensor([kernel_ms, [step_marks[k].elapsed_time(step_marks[k + 1]) for k in range(a.steps)]], dtype=torch.float64, device="cuda")
+    per_rank = [torch.zeros_like(mine) for _ in range(world)]
+    if world > 1:
+        dist.all_gather(per_rank, mine)
+    else:
+        per_rank = [mine]
+    per_rank_ms = {"kernel": [[round(float(v), 2) for v in t[0]] for t in per_rank],
+                   "step": [[round(float(v), 2) for v in t[1]] for t in per_rank]}
     assemble_ms = ev_a0.elapsed_time(ev_a1) if world > 1 else 0.0  # last frame's assembly, incl. waiting for the slowest rank
     assemble_alone_ms = 0.0
     if world > 1:  # the collective by itself, ranks aligned (untimed by the headline)
@@ -351,6 +364,7 @@ def ours(a):
             "l2": "flushed between steps (256 MiB memset)", "parallelism": f"tile-chunk round-robin x{world}, scene replicated",
             "bvh_nodes": info.num_nodes, "bvh_build_ms": info.build_ms, "scene_upload_ms": info.upload_ms,
             "scene_setup_s": setup_s, "seed": 1, "assemble_ms": assemble_ms, "assemble_alone_ms": assemble_alone_ms,
+            "per_rank_ms": per_rank_ms,
         },
         "ms_per_frame": ms_per_step,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_frame": float(e2e_ms[0]),

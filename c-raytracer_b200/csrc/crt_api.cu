@@ -433,12 +433,24 @@ int crt_render_device(crt_scene *s, const crt_render_opts *opts, float *d_raster
 	 * the tail of the persistent grid and keeps a warp's shading points close together */
 	{
 		const uint32_t warps = static_cast<uint32_t>(grid) * kWarpsPerBlock;
-		(void)warps;
 		uint32_t fine = p.num_local_tiles; /* measured: quarter tiles throughout are never slower (profiles/) */
 		if (const char *e = std::getenv("CRT_FINE_PERCENT"))
 			fine = static_cast<uint32_t>(static_cast<uint64_t>(p.num_local_tiles) * std::min(100, std::max(0, std::atoi(e))) / 100u);
 		p.fine_from = p.num_local_tiles - fine;
-		p.num_units = p.fine_from + fine * kTileH;
+		/* the last tiles a few pixels at a time: CRT_MICRO_PER_WARP pixels per resident warp */
+		uint32_t micro_pixels = CRT_MICRO_PIXELS, per_warp = CRT_MICRO_PER_WARP;
+		if (const char *e = std::getenv("CRT_MICRO_PIXELS"))
+			micro_pixels = static_cast<uint32_t>(std::atoi(e));
+		if (const char *e = std::getenv("CRT_MICRO_PER_WARP"))
+			per_warp = static_cast<uint32_t>(std::max(0, std::atoi(e)));
+		if (micro_pixels != 1u && micro_pixels != 2u && micro_pixels != 4u)
+			micro_pixels = CRT_MICRO_PIXELS;
+		const uint32_t tile_pixels = kTileW * kTileH;
+		const uint32_t micro_tiles = static_cast<uint32_t>(std::min<uint64_t>(fine, (static_cast<uint64_t>(warps) * per_warp + tile_pixels - 1) / tile_pixels));
+		p.micro_pixels = micro_pixels;
+		p.micro_tile = p.num_local_tiles - micro_tiles;
+		p.micro_from = p.fine_from + (fine - micro_tiles) * kTileH;
+		p.num_units = p.micro_from + micro_tiles * (tile_pixels / micro_pixels);
 	}
 	p.tile_counter = s->tile_counter;
 	p.counters = s->counters;

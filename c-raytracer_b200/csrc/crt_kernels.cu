@@ -166,10 +166,11 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 
 	for (;;) {
 		/* ---- next tile of this shard ------------------------------------- */
-		/* work unit: a whole 8x4 tile, or -- for the last tiles of the queue, so
-		 * that the frame does not end on a few warps finishing multi-100-ms tiles --
-		 * one 8-pixel row of a tile (lanes 0..7).  A pixel's value does not depend
-		 * on the shape of the unit it is traced in. */
+		/* work unit: a whole 8x4 tile, one 8-pixel row of a tile (lanes 0..7), or --
+		 * for the last tiles of the queue -- one or two pixels: an 8-pixel row through
+		 * the glass mesh is 20 to 100 ms of one warp, which would otherwise be the
+		 * tail of the persistent grid (and 1/8 of a frame has only 14 rows per warp).
+		 * A pixel's value does not depend on the shape of the unit it is traced in. */
 		uint32_t unit = 0;
 		if (lane == 0)
 			unit = atomicAdd(p.tile_counter, 1u);
@@ -178,7 +179,12 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 			break;
 		uint32_t local_tile = unit, pix_lane = lane;
 		bool lane_on = true;
-		if (unit >= p.fine_from) {
+		if (unit >= p.micro_from) {
+			const uint32_t v = unit - p.micro_from, per_tile = (uint32_t)(kTileW * kTileH) / p.micro_pixels;
+			local_tile = p.micro_tile + v / per_tile;
+			pix_lane = (v % per_tile) * p.micro_pixels + lane;
+			lane_on = lane < p.micro_pixels;
+		} else if (unit >= p.fine_from) {
 			const uint32_t v = unit - p.fine_from;
 			local_tile = p.fine_from + v / (uint32_t)kTileH;
 			pix_lane = (v % (uint32_t)kTileH) * (uint32_t)kTileW + lane;

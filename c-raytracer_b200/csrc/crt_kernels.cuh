@@ -28,6 +28,12 @@ constexpr int kBlockThreads = kWarpsPerBlock * 32;
 constexpr int kInnerPerVote = CRT_INNER_PER_VOTE, kPrimPerVote = CRT_PRIM_PER_VOTE; /* unit steps per warp vote */
 constexpr int kInnerWeight = CRT_INNER_WEIGHT, kPrimWeight = CRT_PRIM_WEIGHT;       /* node step iff ready_inner * Wi >= ready_prim * Wp */
 constexpr int kNumCounters = 11;
+#ifndef CRT_MICRO_PIXELS
+#define CRT_MICRO_PIXELS 2                 /* pixels per work unit in the final phase of a frame */
+#endif
+#ifndef CRT_MICRO_PER_WARP
+#define CRT_MICRO_PER_WARP 64              /* pixels per resident warp handed out that way */
+#endif
 #ifndef CRT_MIN_BLOCKS
 #define CRT_MIN_BLOCKS 2                   /* resident render blocks per SM the register budget is set for */
 #endif
@@ -45,7 +51,10 @@ struct RenderParams {
 	uint32_t num_local_tiles;       /* tiles of this shard */
 	uint32_t refill;                /* lanes fetch new shadow rays when fewer than this many are walking */
 	uint32_t fine_from;             /* local tiles from this index on are handed out as 8-pixel rows */
-	uint32_t num_units;             /* work units: fine_from + (num_local_tiles - fine_from) * kTileH */
+	uint32_t micro_from;            /* units from this index on are `micro_pixels` pixels of a tile, tiles from micro_tile on */
+	uint32_t micro_tile;
+	uint32_t micro_pixels;          /* 1, 2 or 4 */
+	uint32_t num_units;             /* fine_from tiles + rows of the next tiles + micro units of the last tiles */
 	unsigned int *tile_counter;
 	unsigned long long *counters;   /* kNumCounters, instrumented instance only */
 	float *pending;                 /* per-lane pending-ray stacks */

@@ -27,6 +27,7 @@ def main():
     ap.add_argument("height", type=int)
     ap.add_argument("--frames", type=int, default=3)
     ap.add_argument("--count", action="store_true", help="also run one instrumented frame first")
+    ap.add_argument("--shards", type=int, default=1, help="render each of N shards in turn on this GPU (what N ranks would do)")
     argv = sys.argv[1:]
     flags = []
     if "--" in argv:
@@ -57,6 +58,15 @@ def main():
         dev.render(o, st)
         ms.append(st.kernel_ms)
     out["kernel_ms"] = ms
+    if a.shards > 1:
+        per = []
+        for i in range(a.shards):
+            o.shard_index, o.shard_count = i, a.shards
+            st = _abi.Stats()
+            dev.render(o, st)
+            per.append(round(st.kernel_ms, 2))
+        out["shard_kernel_ms"] = per
+        out["shards_max_ms"], out["shards_mean_ms"] = max(per), sum(per) / len(per)
     if a.count:
         rays = out["counted"]["rays_closest"] + out["counted"]["rays_shadow"]
         best = min(ms)
