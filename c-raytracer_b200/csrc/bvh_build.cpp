@@ -6,7 +6,10 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <atomic>
+#include <cstdlib>
 #include <cstring>
+#include <thread>
 
 namespace crt {
 
@@ -16,14 +19,30 @@ constexpr int kBins = 16;
 constexpr float kTraversalCost = 1.2f; /* relative to one primitive test */
 constexpr uint32_t kMedianDepth = 40;  /* below this depth: median splits only, bounds the device stack */
 
+/* A subtree set aside while the top of the tree is built: it is built later (by
+ * a worker thread) into its own node vector and spliced in. */
+struct Deferred {
+	uint32_t first, count, depth;
+	std::vector<BvhNode> nodes; /* local pre-order indices */
+	int32_t root = 0;           /* local node index, or encoded leaf */
+	Aabb bounds;
+	uint32_t max_depth = 0;
+};
+
+constexpr int32_t kDeferredBase = 0x40000000; /* child references >= this are indices into Builder::deferred */
+
 struct Builder {
 	const std::vector<Aabb> &boxes;
-	std::vector<float> centroid; /* 3 per box */
+	const std::vector<float> &centroid; /* 3 per box */
 	std::vector<uint32_t> &order;
 	std::vector<BvhNode> &nodes;
 	uint32_t max_depth = 0;
+	/* ranges of at most this many primitives are deferred (0: build everything here) */
+	uint32_t defer_below = 0;
+	std::vector<Deferred> *deferred = nullptr;
 
-	Builder(const std::vector<Aabb> &b, BvhResult &out) : boxes(b), order(out.order), nodes(out.nodes) {}
+	Builder(const std::vector<Aabb> &b, const std::vector<float> &c, std::vector<uint32_t> &o, std::vector<BvhNode> &n)
+		: boxes(b), centroid(c), order(o), nodes(n) {}
 };
 
 inline void box_reset(Aabb &b)
@@ -85,46 +104,65 @@ int32_t build_range(Builder &B, uint32_t first, uint32_t count, uint32_t depth, 
 	}
 	if (count == 1)
 		return encode_leaf(first, 1);
+	if (B.deferred && count <= B.defer_below) {
+		B.deferred->emplace_back();
+		Deferred &d = B.deferred->back();
+		d.first = first;
+		d.count = count;
+		d.depth = depth;
+		return kDeferredBase + static_cast<int32_t>(B.deferred->size() - 1);
+	}
 
 	/* --- choose a split ------------------------------------------------ */
 	int best_axis = -1, best_bin = -1;
 	float best_cost = FLT_MAX;
 	const float parent_area = half_area(bounds);
 	if (depth < kMedianDepth && parent_area > 0.f) {
+		/* one pass over the (permuted, cache-unfriendly) range fills the bins of all three axes */
+		Aabb bin_box[3][kBins];
+		uint32_t bin_count[3][kBins];
+		float scale[3];
+		bool usable[3];
 		for (int axis = 0; axis < 3; axis++) {
 			const float extent = cbox.hi[axis] - cbox.lo[axis];
-			if (!(extent > 0.f))
-				continue;
-			Aabb bin_box[kBins];
-			uint32_t bin_count[kBins];
+			usable[axis] = extent > 0.f;
+			scale[axis] = usable[axis] ? kBins / extent : 0.f;
 			for (int b = 0; b < kBins; b++) {
-				box_reset(bin_box[b]);
-				bin_count[b] = 0;
+				box_reset(bin_box[axis][b]);
+				bin_count[axis][b] = 0;
 			}
-			const float scale = kBins / extent;
-			for (uint32_t i = first; i < first + count; i++) {
-				const uint32_t p = B.order[i];
-				int b = static_cast<int>((B.centroid[3 * p + axis] - cbox.lo[axis]) * scale);
+		}
+		for (uint32_t i = first; i < first + count; i++) {
+			const uint32_t p = B.order[i];
+			const Aabb &pb = B.boxes[p];
+			for (int axis = 0; axis < 3; axis++) {
+				if (!usable[axis])
+					continue;
+				int b = static_cast<int>((B.centroid[3 * p + axis] - cbox.lo[axis]) * scale[axis]);
 				b = std::min(std::max(b, 0), kBins - 1);
-				bin_count[b]++;
-				box_grow(bin_box[b], B.boxes[p]);
+				bin_count[axis][b]++;
+				box_grow(bin_box[axis][b], pb);
 			}
+		}
+		for (int axis = 0; axis < 3; axis++) {
+			if (!usable[axis])
+				continue;
 			float right_area[kBins];
 			uint32_t right_count[kBins];
 			Aabb acc;
 			box_reset(acc);
 			uint32_t n = 0;
 			for (int b = kBins - 1; b > 0; b--) {
-				box_grow(acc, bin_box[b]);
-				n += bin_count[b];
+				box_grow(acc, bin_box[axis][b]);
+				n += bin_count[axis][b];
 				right_area[b] = half_area(acc);
 				right_count[b] = n;
 			}
 			box_reset(acc);
 			n = 0;
 			for (int b = 0; b < kBins - 1; b++) {
-				box_grow(acc, bin_box[b]);
-				n += bin_count[b];
+				box_grow(acc, bin_box[axis][b]);
+				n += bin_count[axis][b];
 				if (n == 0 || right_count[b + 1] == 0)
 					continue;
 				const float cost = half_area(acc) * n + right_area[b + 1] * right_count[b + 1];
@@ -186,6 +224,80 @@ int32_t build_range(Builder &B, uint32_t first, uint32_t count, uint32_t depth, 
 	return id;
 }
 
+/* Copies the top tree and the deferred subtrees into `out` in pre-order (the
+ * numbering of a single-threaded build) and returns the new reference of `ref`.
+ * Child bounds were already known when the top was built. */
+int32_t splice(const std::vector<BvhNode> &top, const std::vector<Deferred> &deferred, int32_t ref, std::vector<BvhNode> &out)
+{
+	if (ref < 0)
+		return ref;
+	if (ref >= kDeferredBase) {
+		const Deferred &d = deferred[ref - kDeferredBase];
+		if (d.root < 0)
+			return d.root;
+		const int32_t base = static_cast<int32_t>(out.size());
+		for (BvhNode n : d.nodes) {
+			for (int c = 0; c < 2; c++)
+				if (n.child[c] >= 0)
+					n.child[c] += base;
+			out.push_back(n);
+		}
+		return base + d.root;
+	}
+	const int32_t id = static_cast<int32_t>(out.size());
+	out.push_back(top[ref]);
+	for (int c = 0; c < 2; c++) {
+		const int32_t r = splice(top, deferred, top[ref].child[c], out);
+		out[id].child[c] = r;
+	}
+	return id;
+}
+
+constexpr uint32_t kForkAbove = 16384; /* smaller ranges are built by the thread that has them */
+
+struct ForkState {
+	uint32_t max_threads;
+	std::atomic<uint32_t> running{ 1 };
+};
+
+/* Builds the subtree of d.first / d.count into d.nodes (local pre-order).  A
+ * large range is split once by the calling thread; its halves are then built
+ * concurrently when a thread is free, one after the other otherwise. */
+void build_subtree(const std::vector<Aabb> &boxes, const std::vector<float> &centroid, std::vector<uint32_t> &order, Deferred &d, ForkState &fork)
+{
+	if (fork.max_threads <= 1 || d.count < kForkAbove) {
+		Builder B(boxes, centroid, order, d.nodes);
+		d.root = build_range(B, d.first, d.count, d.depth, d.bounds);
+		d.max_depth = B.max_depth;
+		return;
+	}
+	/* split this range once: both halves come back deferred */
+	std::vector<BvhNode> top;
+	std::vector<Deferred> halves;
+	halves.reserve(2);
+	Builder B(boxes, centroid, order, top);
+	B.defer_below = d.count - 1;
+	B.deferred = &halves;
+	const int32_t root = build_range(B, d.first, d.count, d.depth, d.bounds);
+	d.max_depth = B.max_depth;
+	if (halves.size() == 2 && fork.running.fetch_add(1) < fork.max_threads) {
+		std::thread other([&]() {
+			build_subtree(boxes, centroid, order, halves[1], fork);
+			fork.running.fetch_sub(1);
+		});
+		build_subtree(boxes, centroid, order, halves[0], fork);
+		other.join();
+	} else {
+		if (halves.size() == 2)
+			fork.running.fetch_sub(1);
+		for (Deferred &h : halves)
+			build_subtree(boxes, centroid, order, h, fork);
+	}
+	for (const Deferred &h : halves)
+		d.max_depth = std::max(d.max_depth, h.max_depth);
+	d.root = splice(top, halves, root, d.nodes);
+}
+
 } // namespace
 
 void build_bvh(const std::vector<Aabb> &boxes, BvhResult &out)
@@ -199,15 +311,29 @@ void build_bvh(const std::vector<Aabb> &boxes, BvhResult &out)
 	out.order.resize(n);
 	for (uint32_t i = 0; i < n; i++)
 		out.order[i] = i;
-	Builder B(boxes, out);
-	B.centroid.resize(3 * static_cast<size_t>(n));
+	std::vector<float> centroid(3 * static_cast<size_t>(n));
 	for (uint32_t i = 0; i < n; i++)
 		for (int k = 0; k < 3; k++)
-			B.centroid[3 * i + k] = 0.5f * (boxes[i].lo[k] + boxes[i].hi[k]);
-	out.nodes.reserve(n);
-
-	Aabb root_box;
-	const int32_t root = build_range(B, 0, n, 1, root_box);
+			centroid[3 * i + k] = 0.5f * (boxes[i].lo[k] + boxes[i].hi[k]);
+	/* Fork-join over the top of the tree: a range is split by one thread, its two
+	 * halves are built concurrently while threads are free (they partition
+	 * disjoint ranges of `order`), and the results are laid out in the pre-order
+	 * a single-threaded build produces, so the tree does not depend on the
+	 * thread count or on the schedule. */
+	uint32_t threads = std::max(1u, std::thread::hardware_concurrency());
+	if (const char *e = std::getenv("CRT_BVH_THREADS"))
+		threads = static_cast<uint32_t>(std::max(1, std::atoi(e)));
+	threads = std::min(threads, 64u);
+	Deferred whole;
+	whole.first = 0;
+	whole.count = n;
+	whole.depth = 1;
+	ForkState fork;
+	fork.max_threads = threads;
+	build_subtree(boxes, centroid, out.order, whole, fork);
+	out.nodes = std::move(whole.nodes);
+	const Aabb root_box = whole.bounds;
+	const int32_t root = whole.root;
 	if (root < 0) {
 		/* the whole scene fits one leaf: wrap it so that node 0 is an inner node */
 		BvhNode node;
@@ -223,7 +349,7 @@ void build_bvh(const std::vector<Aabb> &boxes, BvhResult &out)
 		store_child(node, 1, encode_leaf(0, 1), empty);
 		out.nodes.push_back(node);
 	}
-	out.max_depth = B.max_depth;
+	out.max_depth = whole.max_depth;
 }
 
 /* ---- 8-wide collapse ------------------------------------------------------ */

@@ -1,0 +1,32 @@
+"""Host tree builders (c-raytracer_b200/csrc/bvh_build.cpp): the binned-SAH
+binary tree, its 8-wide collapse and the quantisation, checked by a small C++
+program (tests/bvh_check.cpp) on seeded boxes -- every primitive in exactly one
+leaf (the shadow query tints once per transparent primitive, reference
+accel.c:369-373), boxes contain what is below them, the quantised boxes are
+conservative, the depth fits the device stack, and the multi-threaded build
+gives the single-threaded tree bit for bit."""
+import os
+import subprocess
+
+import pytest
+
+from _util import ROOT
+
+
+@pytest.fixture(scope="module")
+def checker(tmp_path_factory):
+    exe = str(tmp_path_factory.mktemp("bvh") / "bvh_check")
+    csrc = os.path.join(ROOT, "c-raytracer_b200", "csrc")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-I", csrc, os.path.join(ROOT, "tests", "bvh_check.cpp"),
+                    os.path.join(csrc, "bvh_build.cpp"), "-o", exe, "-lpthread"], check=True)
+    return exe
+
+
+@pytest.mark.parametrize("n,seed,kind", [
+    (0, 1, 0), (1, 1, 0), (2, 2, 0), (5, 3, 0), (9, 4, 2), (1000, 5, 0), (1000, 6, 1), (4000, 7, 2),
+    (60000, 8, 0), (60000, 9, 1), (150000, 10, 2),
+])
+def test_tree_invariants(checker, n, seed, kind):
+    r = subprocess.run([checker, str(n), str(seed), str(kind)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.startswith("ok")
