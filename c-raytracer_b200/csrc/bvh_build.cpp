@@ -367,7 +367,16 @@ struct WideBuilder {
 	WideResult &out;
 	std::vector<uint32_t> first, count; /* primitive range of every binary node */
 	uint32_t merge_prims = 0;            /* binary subtrees with at most this many primitives become one leaf */
+	/* optimal collapse (see plan_collapse): per binary node, cost[i - 1] of covering its subtree with at
+	 * most i wide-tree children, and the split that achieves it */
+	std::vector<float> cost;             /* 7 per node */
+	std::vector<uint8_t> split;          /* 8 per node: [0] = children given to the left side when the node is a wide
+	                                        node (8 slots); [i - 1], i = 2..7: left share of i slots, 0 = use i - 1 */
+	bool optimal = false;
+	float prim_cost = 0.35f;             /* one primitive test of a leaf relative to one visit of a wide node */
 };
+
+constexpr uint8_t kPlanLeaf = 255;          /* split[0]: the whole subtree becomes one leaf */
 
 void decode_leaf(int32_t ref, uint32_t &first, uint32_t &count)
 {
@@ -425,31 +434,146 @@ WideRef make_ref(WideBuilder &W, int32_t node, int which)
 	return r;
 }
 
+/* Which binary nodes become 8-wide nodes?  Opening the child with the largest
+ * surface until eight are found (the loop in wide_node) leaves many
+ * bottom-level nodes with two or three children.  Every visit of a wide node
+ * costs the same eight slab tests, so the expected cost of the shadow walk is
+ * the sum over wide nodes of the chance that a ray meets them (their surface):
+ * that sum is minimised exactly by dynamic programming over the binary tree
+ * (Ylitie, Karras, Laine 2017, "Efficient incoherent ray traversal on GPUs
+ * through compressed wide BVHs", section 4.2), with a leaf of P primitives
+ * costing prim_cost * P per ray that meets its box; a binary subtree of at
+ * most merge_prims primitives may become one leaf where that is cheaper:
+ *   C(n, 1) = min( area(n) + min over k of  T(left, k) + T(right, 8 - k),  area(n) * P(n) * prim_cost )
+ *   C(n, i) = min( C(n, i - 1), min over k of  T(left, k) + T(right, i - k) ),  i = 2..7
+ *   T(x, i) = area(x) * P(x) * prim_cost for a binary leaf, C(x, i) for an inner node. */
+float forest_cost(const WideBuilder &W, int32_t ref, uint32_t count, const Aabb &box, int slots)
+{
+	if (ref < 0)
+		return half_area(box) * static_cast<float>(count) * W.prim_cost;
+	return W.cost[7 * static_cast<size_t>(ref) + (slots - 1)];
+}
+
+void plan_collapse(WideBuilder &W)
+{
+	const size_t n = W.bvh.nodes.size();
+	W.cost.assign(7 * n, 0.f);
+	W.split.assign(8 * n, 0);
+	/* children have larger indices than their parent (pre-order): go backwards */
+	for (size_t v = n; v-- > 0;) {
+		const BvhNode &node = W.bvh.nodes[v];
+		int32_t ref[2];
+		uint32_t cnt[2];
+		Aabb cbox[2];
+		Aabb box;
+		for (int k = 0; k < 3; k++) {
+			box.lo[k] = FLT_MAX;
+			box.hi[k] = -FLT_MAX;
+		}
+		for (int c = 0; c < 2; c++) {
+			ref[c] = node.child[c];
+			if (ref[c] < 0) {
+				uint32_t f;
+				decode_leaf(ref[c], f, cnt[c]);
+			} else {
+				cnt[c] = W.count[ref[c]];
+			}
+			const Aabb b = child_box(node, c);
+			cbox[c] = b;
+			if (b.lo[0] >= 1e30f) {
+				cnt[c] = 0; /* the absent child of a one-leaf scene */
+				continue;
+			}
+			for (int k = 0; k < 3; k++) {
+				box.lo[k] = std::min(box.lo[k], b.lo[k]);
+				box.hi[k] = std::max(box.hi[k], b.hi[k]);
+			}
+		}
+		float *cost = &W.cost[7 * v];
+		uint8_t *split = &W.split[8 * v];
+		float best = FLT_MAX;
+		for (int k = 1; k <= 7; k++) {
+			const float c = forest_cost(W, ref[0], cnt[0], cbox[0], k) + forest_cost(W, ref[1], cnt[1], cbox[1], 8 - k);
+			if (c < best) {
+				best = c;
+				split[0] = static_cast<uint8_t>(k);
+			}
+		}
+		cost[0] = half_area(box) + best;
+		const uint32_t prims = cnt[0] + cnt[1];
+		if (prims <= W.merge_prims) {
+			const float as_leaf = half_area(box) * static_cast<float>(prims) * W.prim_cost;
+			if (as_leaf < cost[0]) {
+				cost[0] = as_leaf;
+				split[0] = kPlanLeaf;
+			}
+		}
+		for (int i = 2; i <= 7; i++) {
+			cost[i - 1] = cost[i - 2];
+			split[i - 1] = 0;
+			for (int k = 1; k < i; k++) {
+				const float c = forest_cost(W, ref[0], cnt[0], cbox[0], k) + forest_cost(W, ref[1], cnt[1], cbox[1], i - k);
+				if (c < cost[i - 1]) {
+					cost[i - 1] = c;
+					split[i - 1] = static_cast<uint8_t>(k);
+				}
+			}
+		}
+	}
+}
+
+/* the wide-tree children that cover child `which` of binary node `node` with at most `slots` of them */
+void expand(WideBuilder &W, int32_t node, int which, int slots, std::vector<WideRef> &kids)
+{
+	const WideRef r = make_ref(W, node, which);
+	if (r.ref < 0 && r.box.lo[0] >= 1e30f)
+		return; /* the absent child of a one-leaf scene */
+	if (r.ref < 0) {
+		kids.push_back(r);
+		return;
+	}
+	while (slots > 1 && W.split[8 * static_cast<size_t>(r.ref) + (slots - 1)] == 0)
+		slots--;
+	if (slots == 1) {
+		kids.push_back(r); /* a wide node of its own, or -- split[0] == kPlanLeaf -- one merged leaf */
+		return;
+	}
+	const int k = W.split[8 * static_cast<size_t>(r.ref) + (slots - 1)];
+	expand(W, r.ref, 0, k, kids);
+	expand(W, r.ref, 1, slots - k, kids);
+}
+
 int32_t wide_node(WideBuilder &W, int32_t node, uint32_t depth)
 {
 	W.out.max_depth = std::max(W.out.max_depth, depth);
 	const int32_t id = static_cast<int32_t>(W.out.nodes.size());
 	W.out.nodes.emplace_back();
 	std::vector<WideRef> kids;
-	for (int c = 0; c < 2; c++) {
-		const WideRef r = make_ref(W, node, c);
-		if (!(r.ref < 0 && r.box.lo[0] >= 1e30f))
-			kids.push_back(r);
-	}
-	/* open the binary child with the largest surface that is too big for a wide leaf */
-	while (kids.size() < 8) {
-		int best = -1;
-		float best_area = -1.f;
-		for (size_t i = 0; i < kids.size(); i++)
-			if (kids[i].ref >= 0 && kids[i].count > W.merge_prims && half_area(kids[i].box) > best_area) {
-				best_area = half_area(kids[i].box);
-				best = static_cast<int>(i);
-			}
-		if (best < 0)
-			break;
-		const int32_t open = kids[best].ref;
-		kids[best] = make_ref(W, open, 0);
-		kids.push_back(make_ref(W, open, 1));
+	if (W.optimal) {
+		const int k = W.split[8 * static_cast<size_t>(node)];
+		expand(W, node, 0, k, kids);
+		expand(W, node, 1, 8 - k, kids);
+	} else {
+		for (int c = 0; c < 2; c++) {
+			const WideRef r = make_ref(W, node, c);
+			if (!(r.ref < 0 && r.box.lo[0] >= 1e30f))
+				kids.push_back(r);
+		}
+		/* open the binary child with the largest surface that is too big for a wide leaf */
+		while (kids.size() < 8) {
+			int best = -1;
+			float best_area = -1.f;
+			for (size_t i = 0; i < kids.size(); i++)
+				if (kids[i].ref >= 0 && kids[i].count > W.merge_prims && half_area(kids[i].box) > best_area) {
+					best_area = half_area(kids[i].box);
+					best = static_cast<int>(i);
+				}
+			if (best < 0)
+				break;
+			const int32_t open = kids[best].ref;
+			kids[best] = make_ref(W, open, 0);
+			kids.push_back(make_ref(W, open, 1));
+		}
 	}
 	for (int j = 0; j < 8; j++) {
 		int32_t code = kWideEmpty;
@@ -489,6 +613,12 @@ void build_wide(const BvhResult &bvh, WideResult &out, uint32_t merge_prims)
 	W.first.assign(bvh.nodes.size(), 0);
 	W.count.assign(bvh.nodes.size(), 0);
 	ranges(W, 0);
+	const char *mode = std::getenv("CRT_WIDE_COLLAPSE"); /* "greedy": largest surface first (the round-1 trees) */
+	W.optimal = !(mode && !std::strcmp(mode, "greedy"));
+	if (const char *e = std::getenv("CRT_WIDE_PRIM_COST"))
+		W.prim_cost = static_cast<float>(std::atof(e));
+	if (W.optimal)
+		plan_collapse(W);
 	out.nodes.reserve(bvh.nodes.size() / 2 + 1);
 	wide_node(W, 0, 1);
 }

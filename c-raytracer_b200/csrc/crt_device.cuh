@@ -324,78 +324,14 @@ __device__ __forceinline__ Hit trace_closest(const DScene &sc, const Ray &r, int
 }
 
 /* Any-hit with transmittance: is_light_blocked() (reference render.c:126-134,
- * object.c:183-197, accel.c:360-387).  Returns true at the first opaque
- * occluder closer than dist; every transparent occluder multiplies the light
- * by its kt, once per primitive; the sampled emitter never
- * occludes (accel.c:367). */
-template <bool COUNT>
-__device__ __forceinline__ bool trace_shadow(const DScene &sc, const Ray &r, float dist, int emitter_object,
-	float &lr, float &lg, float &lb, Counters &cn)
-{
-	for (uint32_t k = 0; k < sc.num_planes; k++) {
-		const float4 pl = ldg4(sc.planes + 2 * k);
-		const float4 px = ldg4(sc.planes + 2 * k + 1);
-		float t, a;
-		if (hit_plane<COUNT>(pl, px.x, r, t, a, cn) && t < dist) {
-			const uint32_t info = __float_as_uint(px.y);
-			if (!(info & PRIM_TRANSPARENT))
-				return true;
-			const crt_material *m = sc.materials + (info & PRIM_MATERIAL_MASK);
-			lr *= __ldg(&m->kt[0]);
-			lg *= __ldg(&m->kt[1]);
-			lb *= __ldg(&m->kt[2]);
-		}
-	}
-	if (sc.num_nodes == 0)
-		return false;
-
-	const RayBox rb = make_raybox(r);
-	int stack[kStackSize];
-	int sp = 0;
-	stack[sp++] = kStackSentinel;
-	int node = 0;
-	while (node != kStackSentinel) {
-		while (node >= 0 && node != kStackSentinel) {
-			const float4 *n = sc.nodes + 4 * node;
-			const float4 xy0 = ldg4(n), xy1 = ldg4(n + 1), z01 = ldg4(n + 2);
-			const float4 ch = ldg4(n + 3);
-			bool h0, h1;
-			float t0, t1;
-			test_children(xy0, xy1, z01, r, rb, dist, h0, h1, t0, t1);
-			Cnt<COUNT>::add(cn.box, 2u);
-			const int c0 = __float_as_int(ch.x), c1 = __float_as_int(ch.y);
-			if (!h0 && !h1) {
-				node = stack[--sp];
-			} else {
-				node = h0 ? c0 : c1;
-				if (h0 && h1)
-					stack[sp++] = c1;
-			}
-		}
-		if (node < 0) {
-			const int leaf = ~node;
-			const int first = leaf >> kLeafBits, count = (leaf & ((1 << kLeafBits) - 1)) + 1;
-			for (int i = 0; i < count; i++) {
-				float t;
-				uint32_t info;
-				int object;
-				if (hit_prim<COUNT>(sc, first + i, r, t, info, object, cn) && t < dist && object != emitter_object) {
-					if (!(info & PRIM_TRANSPARENT))
-						return true;
-					const crt_material *m = sc.materials + (info & PRIM_MATERIAL_MASK);
-					lr *= __ldg(&m->kt[0]);
-					lg *= __ldg(&m->kt[1]);
-					lb *= __ldg(&m->kt[2]);
-				}
-			}
-			node = stack[--sp];
-		}
-	}
-	return false;
-}
-
-/* trace_shadow() in resumable pieces for the render kernel's refilling lanes:
- * shadow_planes() is the linear plane scan, the ShadowWalk steps below walk the BVH. */
+ * object.c:183-197, accel.c:360-387).  Blocked at the first opaque occluder
+ * closer than dist; every transparent occluder multiplies the light by its
+ * kt, once per primitive; the sampled emitter never occludes
+ * (accel.c:367).  It runs in resumable pieces, so that the render kernel's
+ * lanes can be refilled and scheduled step by step:
+ * shadow_planes() is the linear plane scan, the ShadowWalk steps below walk
+ * the quantised 8-wide tree; trace_shadow_wide() strings them together for
+ * one ray per thread (the crt_trace_shadow seam). */
 template <bool COUNT>
 __device__ __forceinline__ bool shadow_planes(const DScene &sc, const Ray &r, float dist, float &lr, float &lg, float &lb, Counters &cn)
 {
