@@ -248,6 +248,16 @@ struct Scratch {
 	~Scratch() { cudaFree(p); }
 };
 
+/* a timing event that is released on every return path */
+struct Event {
+	cudaEvent_t e = nullptr;
+	~Event()
+	{
+		if (e)
+			cudaEventDestroy(e);
+	}
+};
+
 /* Scratch of the depth-of-field kernels, kept per device between calls (a
  * cudaMalloc / cudaFree pair per frame costs more than the kernels).  Calls
  * that reuse it are ordered on the device by an event: the next call's stream
@@ -326,11 +336,11 @@ int crt_postprocess_device(int device, const crt_post_opts *opts, uint32_t width
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
 	const size_t pixels = (size_t)width * height;
 	crt_post_stats st{};
-	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	Event ev0, ev1;
 	if (stats) {
-		POST_TRY(cudaEventCreate(&ev0));
-		POST_TRY(cudaEventCreate(&ev1));
-		POST_TRY(cudaEventRecord(ev0, stream));
+		POST_TRY(cudaEventCreate(&ev0.e));
+		POST_TRY(cudaEventCreate(&ev1.e));
+		POST_TRY(cudaEventRecord(ev0.e, stream));
 	}
 
 	PointOps before{}, after{};
@@ -420,11 +430,9 @@ int crt_postprocess_device(int device, const crt_post_opts *opts, uint32_t width
 	}
 	if (stats) {
 		float ms = 0.f;
-		POST_TRY(cudaEventRecord(ev1, stream));
-		POST_TRY(cudaEventSynchronize(ev1));
-		POST_TRY(cudaEventElapsedTime(&ms, ev0, ev1));
-		cudaEventDestroy(ev0);
-		cudaEventDestroy(ev1);
+		POST_TRY(cudaEventRecord(ev1.e, stream));
+		POST_TRY(cudaEventSynchronize(ev1.e));
+		POST_TRY(cudaEventElapsedTime(&ms, ev0.e, ev1.e));
 		st.kernel_ms = ms;
 		st.total_ms = ms;
 		*stats = st;
@@ -443,10 +451,10 @@ int crt_postprocess(int device, const crt_post_opts *opts, uint32_t width, uint3
 	if (rc)
 		return rc;
 	const size_t pixels = (size_t)width * height;
-	cudaEvent_t ev0, ev1;
-	POST_TRY(cudaEventCreate(&ev0));
-	POST_TRY(cudaEventCreate(&ev1));
-	POST_TRY(cudaEventRecord(ev0, nullptr));
+	Event ev0, ev1;
+	POST_TRY(cudaEventCreate(&ev0.e));
+	POST_TRY(cudaEventCreate(&ev1.e));
+	POST_TRY(cudaEventRecord(ev0.e, nullptr));
 	Scratch d_raster, d_z;
 	POST_TRY(cudaMalloc(&d_raster.p, pixels * 3 * sizeof(float)));
 	POST_TRY(cudaMalloc(&d_z.p, pixels * sizeof(float)));
@@ -458,11 +466,9 @@ int crt_postprocess(int device, const crt_post_opts *opts, uint32_t width, uint3
 		return rc;
 	POST_TRY(cudaMemcpy(raster, d_raster.p, pixels * 3 * sizeof(float), cudaMemcpyDeviceToHost));
 	float ms = 0.f;
-	POST_TRY(cudaEventRecord(ev1, nullptr));
-	POST_TRY(cudaEventSynchronize(ev1));
-	POST_TRY(cudaEventElapsedTime(&ms, ev0, ev1));
-	cudaEventDestroy(ev0);
-	cudaEventDestroy(ev1);
+	POST_TRY(cudaEventRecord(ev1.e, nullptr));
+	POST_TRY(cudaEventSynchronize(ev1.e));
+	POST_TRY(cudaEventElapsedTime(&ms, ev0.e, ev1.e));
 	st.total_ms = ms;
 	if (stats)
 		*stats = st;
