@@ -373,6 +373,7 @@ struct WideBuilder {
 	std::vector<uint8_t> split;          /* 8 per node: [0] = children given to the left side when the node is a wide
 	                                        node (8 slots); [i - 1], i = 2..7: left share of i slots, 0 = use i - 1 */
 	bool optimal = false;
+	bool order_by_area = false;
 	float prim_cost = 0.35f;             /* one primitive test of a leaf relative to one visit of a wide node */
 };
 
@@ -575,6 +576,11 @@ int32_t wide_node(WideBuilder &W, int32_t node, uint32_t depth)
 			kids.push_back(make_ref(W, open, 1));
 		}
 	}
+	/* experiment (CRT_WIDE_ORDER=area, off by default): children are pushed in slot order and
+	 * popped in reverse, so the largest boxes last = visited first, which finds an opaque
+	 * occluder sooner; any-hit results do not depend on the order */
+	if (W.order_by_area)
+		std::stable_sort(kids.begin(), kids.end(), [](const WideRef &a, const WideRef &b) { return half_area(a.box) < half_area(b.box); });
 	for (int j = 0; j < 8; j++) {
 		int32_t code = kWideEmpty;
 		Aabb box;
@@ -615,6 +621,8 @@ void build_wide(const BvhResult &bvh, WideResult &out, uint32_t merge_prims)
 	ranges(W, 0);
 	const char *mode = std::getenv("CRT_WIDE_COLLAPSE"); /* "greedy": largest surface first (the round-1 trees) */
 	W.optimal = !(mode && !std::strcmp(mode, "greedy"));
+	if (const char *e = std::getenv("CRT_WIDE_ORDER"))
+		W.order_by_area = !std::strcmp(e, "area");
 	if (const char *e = std::getenv("CRT_WIDE_PRIM_COST"))
 		W.prim_cost = static_cast<float>(std::atof(e));
 	if (W.optimal)

@@ -36,6 +36,10 @@ constexpr uint32_t PRIM_MATERIAL_MASK = 0x00ffffffu;
 constexpr int kStackSize = 128;         /* >= binary tree depth (closest hit) and 7 * wide tree depth + 1 (shadow walk): checked at scene creation */
 constexpr int kStackSentinel = 0x7fffffff;
 constexpr int kLeafBits = 3;
+#ifndef CRT_WIDE_NODE_STRIDE
+#define CRT_WIDE_NODE_STRIDE 6             /* float4 per quantised node in memory: 6 = packed (96 B), 8 = one 128-byte line each */
+#endif
+constexpr int kWideStride = CRT_WIDE_NODE_STRIDE;
 constexpr float kPi = 3.1415927f;       /* reference src/core/type.h:30 */
 
 struct DEmitter {
@@ -453,7 +457,7 @@ template <bool COUNT, class QUEUE>
 __device__ __forceinline__ void shadow_inner_step(const DScene &sc, const Ray &r, const RayWide &rw, float dist, ShadowWalk &w,
 	int *stack, const QUEUE &q, Counters &cn)
 {
-	const float4 *n = sc.wide + 6 * (size_t)w.node;
+	const float4 *n = sc.wide + kWideStride * (size_t)w.node;
 	const float4 w0 = ldg4(n), w1 = ldg4(n + 1), w2 = ldg4(n + 2), w3 = ldg4(n + 3), w4 = ldg4(n + 4), w5 = ldg4(n + 5);
 	const uint32_t eb = __float_as_uint(w0.w);
 	const float adjx = __uint_as_float((eb & 0xffu) << 23) * rw.idx;
