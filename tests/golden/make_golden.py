@@ -51,6 +51,9 @@ IMAGE_CASES = [
     ("scene4_b1_seed7", "scene4", 48, 27, ("-b", "1", "--seed", "7")),
     ("scenetest_rnorm", "scenetest", 48, 27, ("-r", "norm")),
     ("scene2_odd_size", "scene2", 37, 23, ()),
+    # scenetest3: a triangle emitter, two sphere emitters with different sample counts and colours (object.c:293-304, :403-419)
+    ("scenetest3_ambient", "scenetest3", 64, 36, ()),
+    ("scenetest3_path2", "scenetest3", 48, 27, ("-g", "path", "-n", "2", "--seed", "4")),
 ]
 
 RAY_SCENES = ["scene1", "scene3", "scene4", "scenetest", "scenetest2", "scene5_small", "scene6_small"]
@@ -90,13 +93,18 @@ def main():
         sys.exit("oracle/_ref/ref_engine is missing: run `make -C oracle ref` where /root/reference exists")
     rng = np.random.default_rng(20240607)
 
+    only = os.environ.get("GOLDEN_ONLY")  # e.g. GOLDEN_ONLY=scenetest3 adds fixtures without touching the others
     for name, scene, w, h, flags in IMAGE_CASES:
+        if only and only not in name:
+            continue
         raster, z, cnt = oracle.ref_render(os.path.join("scenes", scene + ".json"), w, h, flags, seed=seed_of(flags))
         np.savez_compressed(os.path.join(HERE, f"image_{name}.npz"), raster=raster, z=z,
                             cast_ray=cnt["cast_ray"], shadow=cnt["shadow"], scene=scene, width=w, height=h,
                             flags=np.array(flags, dtype=str))
         print(f"image_{name}: {w}x{h} cast_ray {cnt['cast_ray']} shadow {cnt['shadow']} max {raster.max():.4f}")
 
+    if only:
+        return
     for scene in RAY_SCENES:
         sc = host.Scene(os.path.join(ROOT, "scenes", scene + ".json"))
         rays, dist, emitter, light = make_rays(sc, rng, N_RAYS)
