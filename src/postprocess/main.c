@@ -61,7 +61,7 @@ int main(int argc, char *argv[])
 	/* the checks of postprocess/image.c:48-50, :68 */
 	if (in.bits_per_sample != 32 || !in.raster)
 		rt_fatal("Expected 32 bits per sample but got [%u].", in.bits_per_sample);
-	if (!in.z_buffer || in.z_count != (uint32_t)((size_t)in.width * in.height))
+	if (!in.z_buffer || (uint64_t)in.z_count != (uint64_t)in.width * in.height)
 		rt_fatal("Corrupted Z-Buffer.");
 
 	crt_post_opts opts;

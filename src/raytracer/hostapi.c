@@ -78,7 +78,7 @@ int rt_host_load_raw(const char *filename, unsigned *width, unsigned *height, fl
 	struct rt_tiff_image img;
 	if (rt_tiff_read(filename, &img, last_error))
 		return -1;
-	if (img.bits_per_sample != 32 || !img.raster || !img.z_buffer || img.z_count != (uint32_t)((size_t)img.width * img.height)) {
+	if (img.bits_per_sample != 32 || !img.raster || !img.z_buffer || (uint64_t)img.z_count != (uint64_t)img.width * img.height) {
 		snprintf(last_error, sizeof last_error, "[%s] is not a raw frame (32 bits per sample with a z-buffer)", filename);
 		rt_tiff_free(&img);
 		return -1;

@@ -221,8 +221,15 @@ int rt_tiff_read(const char *filename, struct rt_tiff_image *img, char *err)
 	}
 
 	img->bits_per_sample = bits;
-	const size_t row_bytes = (size_t)img->width * 3u * (bits / 8u);
-	uint8_t *pixels = malloc(row_bytes * img->height);
+	/* Width and height come from the file: the pixel data of an uncompressed image cannot be
+	 * larger than the file itself, which also keeps row_bytes * height far from wrapping. */
+	const uint64_t row_bytes64 = (uint64_t)img->width * 3u * (bits / 8u);
+	if (row_bytes64 > (uint64_t)r.size || (uint64_t)img->height > (uint64_t)r.size / row_bytes64) {
+		free(data);
+		rt_fail(err, "Image dimensions %ux%u of [%s] exceed the file size.", img->width, img->height, filename);
+	}
+	const size_t row_bytes = (size_t)row_bytes64;
+	uint8_t *pixels = calloc(row_bytes * img->height, 1);
 	if (!pixels) {
 		free(data);
 		rt_fail(err, "Unable to allocate image [%s].", filename);
@@ -240,13 +247,18 @@ int rt_tiff_read(const char *filename, struct rt_tiff_image *img, char *err)
 			if (c < bytes)
 				bytes = c;
 		}
-		if (off + bytes > r.size) {
+		if (off > r.size || bytes > r.size - off) {
 			free(pixels);
 			free(data);
 			rt_fail(err, "Truncated strip in [%s].", filename);
 		}
 		memcpy(pixels + row_bytes * row, data + off, bytes);
 		row += rows;
+	}
+	if (row < img->height) {
+		free(pixels);
+		free(data);
+		rt_fail(err, "Strips of [%s] cover %u of %u rows.", filename, row, img->height);
 	}
 	if (bits == 32 && r.big_endian) {
 		for (size_t i = 0; i + 3 < row_bytes * img->height; i += 4) {
@@ -262,12 +274,19 @@ int rt_tiff_read(const char *filename, struct rt_tiff_image *img, char *err)
 	if (e_z) {
 		img->z_count = rd(&r, e_z + 4, 4);
 		const size_t off = img->z_count == 1 ? e_z + 8 : rd(&r, e_z + 8, 4);
-		if (off + 4ull * img->z_count > r.size) {
+		/* one depth per pixel, compared in 64 bits (a wrapped product must not pass) */
+		if ((uint64_t)img->z_count != (uint64_t)img->width * img->height || off > r.size ||
+		    4ull * img->z_count > r.size - off) {
 			free(data);
 			rt_tiff_free(img);
 			rt_fail(err, "Corrupted Z-Buffer.");
 		}
 		img->z_buffer = malloc(4ull * (img->z_count ? img->z_count : 1));
+		if (!img->z_buffer) {
+			free(data);
+			rt_tiff_free(img);
+			rt_fail(err, "Unable to allocate the Z-Buffer of [%s].", filename);
+		}
 		for (uint32_t i = 0; i < img->z_count; i++) {
 			const uint32_t bitsv = rd(&r, off + 4ull * i, 4);
 			memcpy(&img->z_buffer[i], &bitsv, 4);

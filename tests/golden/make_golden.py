@@ -56,6 +56,18 @@ IMAGE_CASES = [
     ("scenetest3_path2", "scenetest3", 48, 27, ("-g", "path", "-n", "2", "--seed", "4")),
 ]
 
+# The benchmark workloads' own flags on the benchmark geometry (bench.py: scene5 -g path -n 16;
+# configs[4]: scene6 path traced), at a frame size the reference renders in minutes.  Written as
+# bench_<name>.npz (not image_*: the CPU suite does not run the oracle on them) by
+#     GOLDEN_BENCH=1 python tests/golden/make_golden.py
+# Besides the frame, each file holds the SHA-256 of the (generated, tools/gen_meshes.py) mesh it was
+# rendered from and the reference's own seed-to-seed rel-RMSE at the same flags (seed 1 against
+# seed 2): SURVEY 8(d) Tier 2 bounds a stochastic configuration by twice that number.
+BENCH_CASES = [
+    ("scene5_n16", "scene5", 480, 270, ("-g", "path", "-n", "16"), "meshes/dragon.stl"),
+    ("scene6_n4", "scene6", 480, 270, ("-g", "path", "-n", "4"), "meshes/menger_sponge.stl"),
+]
+
 RAY_SCENES = ["scene1", "scene3", "scene4", "scenetest", "scenetest2", "scene5_small", "scene6_small"]
 N_RAYS = 1500
 
@@ -92,6 +104,22 @@ def main():
     if not oracle.have_ref():
         sys.exit("oracle/_ref/ref_engine is missing: run `make -C oracle ref` where /root/reference exists")
     rng = np.random.default_rng(20240607)
+
+    if os.environ.get("GOLDEN_BENCH"):
+        import hashlib
+        for name, scene, w, h, flags, mesh in BENCH_CASES:
+            path = os.path.join("scenes", scene + ".json")
+            raster, z, cnt = oracle.ref_render(path, w, h, flags, seed=1)
+            other, _, _ = oracle.ref_render(path, w, h, flags, seed=2)
+            seed_rmse = float(np.linalg.norm(other.astype(np.float64) - raster) / np.linalg.norm(raster.astype(np.float64)))
+            sha = hashlib.sha256(open(os.path.join(ROOT, mesh), "rb").read()).hexdigest()
+            np.savez_compressed(os.path.join(HERE, f"bench_{name}.npz"), raster=raster, z=z,
+                                cast_ray=cnt["cast_ray"], shadow=cnt["shadow"], scene=scene, width=w, height=h,
+                                flags=np.array(flags, dtype=str), seed_to_seed_rel_rmse=seed_rmse,
+                                mesh=mesh, mesh_sha256=sha, ref_seconds=cnt["seconds"])
+            print(f"bench_{name}: {w}x{h} cast_ray {cnt['cast_ray']} shadow {cnt['shadow']} "
+                  f"seed-to-seed rel-RMSE {seed_rmse:.4e} ({cnt['seconds']:.1f} s per frame)")
+        return
 
     only = os.environ.get("GOLDEN_ONLY")  # e.g. GOLDEN_ONLY=scenetest3 adds fixtures without touching the others
     for name, scene, w, h, flags in IMAGE_CASES:

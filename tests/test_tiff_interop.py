@@ -158,6 +158,55 @@ def test_truncated_and_foreign_files_are_rejected(tmp_path):
         host.load_raw(str(tmp_path / "missing.tif"))
 
 
+def _patch_ifd(blob, tag, value):
+    """Overwrites the inline value of one IFD entry of a little-endian classic TIFF."""
+    b = bytearray(blob)
+    ifd = struct.unpack_from("<I", b, 4)[0]
+    for i in range(struct.unpack_from("<H", b, ifd)[0]):
+        e = ifd + 2 + 12 * i
+        if struct.unpack_from("<H", b, e)[0] == tag:
+            typ = struct.unpack_from("<H", b, e + 2)[0]
+            struct.pack_into("<H" if typ == 3 else "<I", b, e + 8, value)
+            return bytes(b)
+    raise KeyError(tag)
+
+
+def test_crafted_dimensions_are_rejected(tmp_path):
+    """Width and height come from the file: a frame whose pixel data cannot fit the file, whose
+    width * height wraps 32 bits, or whose strips do not cover every row must be refused
+    instead of copied past a short allocation."""
+    rng = np.random.default_rng(3)
+    raster = rng.random((6, 5, 3), dtype=np.float32)
+    z = rng.random((6, 5), dtype=np.float32)
+    good = str(tmp_path / "good.tif")
+    synth_tiff(good, raster, z, "<", 1, True, False, True)
+    b = open(good, "rb").read()
+    host.load_raw(good)
+    cases = {
+        "wide.tif": _patch_ifd(b, 256, 0x80000000),                           # 12 * w * h wraps a 64-bit size_t with the next one
+        "wrap.tif": _patch_ifd(_patch_ifd(b, 256, 0x80000000), 257, 0x80000000),
+        "wrap32.tif": _patch_ifd(_patch_ifd(b, 256, 0x10000), 257, 0x10000),  # w * h == 0 mod 2^32
+        "tall.tif": _patch_ifd(b, 257, 7),                                    # one row more than there are strips
+    }
+    for name, data in cases.items():
+        q = str(tmp_path / name)
+        open(q, "wb").write(data)
+        with pytest.raises(host.SceneError):
+            host.load_raw(q)
+    # fewer strips than rows: rows_per_strip says 1, the strip table holds 6 entries, height claims 6 but
+    # the table is cut to 5 by patching its count
+    bb = bytearray(b)
+    ifd = struct.unpack_from("<I", bb, 4)[0]
+    for i in range(struct.unpack_from("<H", bb, ifd)[0]):
+        e = ifd + 2 + 12 * i
+        if struct.unpack_from("<H", bb, e)[0] in (273, 279):
+            struct.pack_into("<I", bb, e + 4, 5)
+    q = str(tmp_path / "fewstrips.tif")
+    open(q, "wb").write(bytes(bb))
+    with pytest.raises(host.SceneError, match="rows"):
+        host.load_raw(q)
+
+
 def test_postprocess_cli_usage_without_gpu(tmp_path):
     """Argument handling of the `postprocess` executable that ends before any GPU work
     (reference src/postprocess/main.c:46-60)."""
