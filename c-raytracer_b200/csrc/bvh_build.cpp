@@ -354,37 +354,72 @@ void build_bvh(const std::vector<Aabb> &boxes, BvhResult &out)
 
 /* ---- 8-wide collapse ------------------------------------------------------ */
 
+uint16_t half_bits(float f)
+{
+	uint32_t x;
+	std::memcpy(&x, &f, 4);
+	const uint32_t sign = (x >> 16) & 0x8000u;
+	const int32_t exp = static_cast<int32_t>((x >> 23) & 0xffu) - 127 + 15;
+	uint32_t man = x & 0x7fffffu;
+	if (((x >> 23) & 0xffu) == 0xffu)
+		return static_cast<uint16_t>(sign | 0x7c00u | (man ? 0x200u : 0u));
+	if (exp >= 31)
+		return static_cast<uint16_t>(sign | 0x7c00u);
+	if (exp <= 0) {
+		if (exp < -10)
+			return static_cast<uint16_t>(sign);
+		man |= 0x800000u;
+		const int shift = 14 - exp;
+		uint32_t h = man >> shift;
+		const uint32_t rem = man & ((1u << shift) - 1u), half = 1u << (shift - 1);
+		if (rem > half || (rem == half && (h & 1u)))
+			h++;
+		return static_cast<uint16_t>(sign | h);
+	}
+	uint32_t h = (static_cast<uint32_t>(exp) << 10) | (man >> 13);
+	const uint32_t rem = man & 0x1fffu;
+	if (rem > 0x1000u || (rem == 0x1000u && (h & 1u)))
+		h++;
+	return static_cast<uint16_t>(sign | h);
+}
+
+float half_value(uint16_t h)
+{
+	const uint32_t sign = (h & 0x8000u) << 16, exp = (h >> 10) & 0x1fu, man = h & 0x3ffu;
+	float f;
+	if (exp == 0) {
+		f = std::ldexp(static_cast<float>(man), -24);
+	} else if (exp == 31) {
+		uint32_t x = 0x7f800000u | (man << 13);
+		std::memcpy(&f, &x, 4);
+	} else {
+		f = std::ldexp(static_cast<float>(man | 0x400u), static_cast<int>(exp) - 25);
+	}
+	uint32_t x;
+	std::memcpy(&x, &f, 4);
+	x |= sign;
+	std::memcpy(&f, &x, 4);
+	return f;
+}
+
 namespace {
 
 struct WideRef {
 	int32_t ref; /* binary node index, or encoded leaf */
 	Aabb box;
-	uint32_t first, count;
 };
 
 struct WideBuilder {
 	const BvhResult &bvh;
-	WideResult &out;
-	std::vector<uint32_t> first, count; /* primitive range of every binary node */
-	uint32_t merge_prims = 0;            /* binary subtrees with at most this many primitives become one leaf */
+	WideTree &out;
 	/* optimal collapse (see plan_collapse): per binary node, cost[i - 1] of covering its subtree with at
 	 * most i wide-tree children, and the split that achieves it */
-	std::vector<float> cost;             /* 7 per node */
-	std::vector<uint8_t> split;          /* 8 per node: [0] = children given to the left side when the node is a wide
-	                                        node (8 slots); [i - 1], i = 2..7: left share of i slots, 0 = use i - 1 */
-	bool optimal = false;
-	bool order_by_area = false;
-	float prim_cost = 0.35f;             /* one primitive test of a leaf relative to one visit of a wide node */
+	std::vector<float> cost;    /* 7 per node */
+	std::vector<uint8_t> split; /* 8 per node: [0] = children given to the left side when the node is a wide
+	                               node (8 slots); [i - 1], i = 2..7: left share of i slots, 0 = use i - 1 */
+	float prim_cost = 0.6f;     /* one primitive test relative to one visit of a wide node */
+	uint32_t next_prim = 0;
 };
-
-constexpr uint8_t kPlanLeaf = 255;          /* split[0]: the whole subtree becomes one leaf */
-
-void decode_leaf(int32_t ref, uint32_t &first, uint32_t &count)
-{
-	const uint32_t leaf = static_cast<uint32_t>(~ref);
-	first = leaf >> kLeafCountBits;
-	count = (leaf & ((1u << kLeafCountBits) - 1u)) + 1u;
-}
 
 Aabb child_box(const BvhNode &n, int which)
 {
@@ -399,59 +434,25 @@ Aabb child_box(const BvhNode &n, int which)
 	return b;
 }
 
-void ranges(WideBuilder &W, int32_t node)
+bool absent(const Aabb &b)
 {
-	uint32_t lo = 0xffffffffu, total = 0;
-	for (int c = 0; c < 2; c++) {
-		const int32_t ref = W.bvh.nodes[node].child[c];
-		uint32_t f, n;
-		if (ref < 0) {
-			decode_leaf(ref, f, n);
-			if (child_box(W.bvh.nodes[node], c).lo[0] >= 1e30f)
-				continue; /* the absent child of a one-leaf scene */
-		} else {
-			ranges(W, ref);
-			f = W.first[ref];
-			n = W.count[ref];
-		}
-		lo = std::min(lo, f);
-		total += n;
-	}
-	W.first[node] = lo;
-	W.count[node] = total;
+	return b.lo[0] >= 1e30f; /* the second child of a one-primitive scene */
 }
 
-WideRef make_ref(WideBuilder &W, int32_t node, int which)
-{
-	WideRef r;
-	r.ref = W.bvh.nodes[node].child[which];
-	r.box = child_box(W.bvh.nodes[node], which);
-	if (r.ref < 0) {
-		decode_leaf(r.ref, r.first, r.count);
-	} else {
-		r.first = W.first[r.ref];
-		r.count = W.count[r.ref];
-	}
-	return r;
-}
-
-/* Which binary nodes become 8-wide nodes?  Opening the child with the largest
- * surface until eight are found (the loop in wide_node) leaves many
- * bottom-level nodes with two or three children.  Every visit of a wide node
- * costs the same eight slab tests, so the expected cost of the shadow walk is
- * the sum over wide nodes of the chance that a ray meets them (their surface):
- * that sum is minimised exactly by dynamic programming over the binary tree
- * (Ylitie, Karras, Laine 2017, "Efficient incoherent ray traversal on GPUs
- * through compressed wide BVHs", section 4.2), with a leaf of P primitives
- * costing prim_cost * P per ray that meets its box; a binary subtree of at
- * most merge_prims primitives may become one leaf where that is cheaper:
- *   C(n, 1) = min( area(n) + min over k of  T(left, k) + T(right, 8 - k),  area(n) * P(n) * prim_cost )
+/* Which binary nodes become 8-wide nodes?  Every visit of a wide node costs the
+ * same eight slab tests, so the expected cost of a walk is the sum over wide
+ * nodes of the chance that a ray meets them (their surface) plus, for every
+ * primitive, prim_cost times the surface of its box.  That sum is minimised
+ * exactly by dynamic programming over the binary tree (Ylitie, Karras, Laine
+ * 2017, "Efficient incoherent ray traversal on GPUs through compressed wide
+ * BVHs", section 4.2):
+ *   C(n, 1) = area(n) + min over k of  T(left, k) + T(right, 8 - k)
  *   C(n, i) = min( C(n, i - 1), min over k of  T(left, k) + T(right, i - k) ),  i = 2..7
- *   T(x, i) = area(x) * P(x) * prim_cost for a binary leaf, C(x, i) for an inner node. */
-float forest_cost(const WideBuilder &W, int32_t ref, uint32_t count, const Aabb &box, int slots)
+ *   T(x, i) = area(x) * prim_cost for a leaf (one primitive), C(x, i) for an inner node. */
+float forest_cost(const WideBuilder &W, int32_t ref, const Aabb &box, int slots)
 {
 	if (ref < 0)
-		return half_area(box) * static_cast<float>(count) * W.prim_cost;
+		return absent(box) ? 0.f : half_area(box) * W.prim_cost;
 	return W.cost[7 * static_cast<size_t>(ref) + (slots - 1)];
 }
 
@@ -463,57 +464,29 @@ void plan_collapse(WideBuilder &W)
 	/* children have larger indices than their parent (pre-order): go backwards */
 	for (size_t v = n; v-- > 0;) {
 		const BvhNode &node = W.bvh.nodes[v];
-		int32_t ref[2];
-		uint32_t cnt[2];
-		Aabb cbox[2];
+		const int32_t ref[2] = { node.child[0], node.child[1] };
+		const Aabb cbox[2] = { child_box(node, 0), child_box(node, 1) };
 		Aabb box;
-		for (int k = 0; k < 3; k++) {
-			box.lo[k] = FLT_MAX;
-			box.hi[k] = -FLT_MAX;
-		}
-		for (int c = 0; c < 2; c++) {
-			ref[c] = node.child[c];
-			if (ref[c] < 0) {
-				uint32_t f;
-				decode_leaf(ref[c], f, cnt[c]);
-			} else {
-				cnt[c] = W.count[ref[c]];
-			}
-			const Aabb b = child_box(node, c);
-			cbox[c] = b;
-			if (b.lo[0] >= 1e30f) {
-				cnt[c] = 0; /* the absent child of a one-leaf scene */
-				continue;
-			}
-			for (int k = 0; k < 3; k++) {
-				box.lo[k] = std::min(box.lo[k], b.lo[k]);
-				box.hi[k] = std::max(box.hi[k], b.hi[k]);
-			}
-		}
+		box_reset(box);
+		for (int c = 0; c < 2; c++)
+			if (!absent(cbox[c]))
+				box_grow(box, cbox[c]);
 		float *cost = &W.cost[7 * v];
 		uint8_t *split = &W.split[8 * v];
 		float best = FLT_MAX;
 		for (int k = 1; k <= 7; k++) {
-			const float c = forest_cost(W, ref[0], cnt[0], cbox[0], k) + forest_cost(W, ref[1], cnt[1], cbox[1], 8 - k);
+			const float c = forest_cost(W, ref[0], cbox[0], k) + forest_cost(W, ref[1], cbox[1], 8 - k);
 			if (c < best) {
 				best = c;
 				split[0] = static_cast<uint8_t>(k);
 			}
 		}
 		cost[0] = half_area(box) + best;
-		const uint32_t prims = cnt[0] + cnt[1];
-		if (prims <= W.merge_prims) {
-			const float as_leaf = half_area(box) * static_cast<float>(prims) * W.prim_cost;
-			if (as_leaf < cost[0]) {
-				cost[0] = as_leaf;
-				split[0] = kPlanLeaf;
-			}
-		}
 		for (int i = 2; i <= 7; i++) {
 			cost[i - 1] = cost[i - 2];
 			split[i - 1] = 0;
 			for (int k = 1; k < i; k++) {
-				const float c = forest_cost(W, ref[0], cnt[0], cbox[0], k) + forest_cost(W, ref[1], cnt[1], cbox[1], i - k);
+				const float c = forest_cost(W, ref[0], cbox[0], k) + forest_cost(W, ref[1], cbox[1], i - k);
 				if (c < cost[i - 1]) {
 					cost[i - 1] = c;
 					split[i - 1] = static_cast<uint8_t>(k);
@@ -524,19 +497,20 @@ void plan_collapse(WideBuilder &W)
 }
 
 /* the wide-tree children that cover child `which` of binary node `node` with at most `slots` of them */
-void expand(WideBuilder &W, int32_t node, int which, int slots, std::vector<WideRef> &kids)
+void expand(const WideBuilder &W, int32_t node, int which, int slots, std::vector<WideRef> &kids)
 {
-	const WideRef r = make_ref(W, node, which);
-	if (r.ref < 0 && r.box.lo[0] >= 1e30f)
-		return; /* the absent child of a one-leaf scene */
+	WideRef r;
+	r.ref = W.bvh.nodes[node].child[which];
+	r.box = child_box(W.bvh.nodes[node], which);
 	if (r.ref < 0) {
-		kids.push_back(r);
+		if (!absent(r.box))
+			kids.push_back(r);
 		return;
 	}
 	while (slots > 1 && W.split[8 * static_cast<size_t>(r.ref) + (slots - 1)] == 0)
 		slots--;
 	if (slots == 1) {
-		kids.push_back(r); /* a wide node of its own, or -- split[0] == kPlanLeaf -- one merged leaf */
+		kids.push_back(r); /* a wide node of its own */
 		return;
 	}
 	const int k = W.split[8 * static_cast<size_t>(r.ref) + (slots - 1)];
@@ -544,175 +518,137 @@ void expand(WideBuilder &W, int32_t node, int which, int slots, std::vector<Wide
 	expand(W, r.ref, 1, slots - k, kids);
 }
 
-int32_t wide_node(WideBuilder &W, int32_t node, uint32_t depth)
+/* Grid of a node: origin = lower corner of the union of the child boxes, scale = the
+ * smallest power of two with extent <= (kWideGrid - 1) * scale on every axis.  Child
+ * planes are rounded outwards to grid lines in exact (double) arithmetic. */
+void quantize_node(WideNode &n, const std::vector<WideRef> &kids, const std::vector<int> &slot_of)
+{
+	Aabb box;
+	box_reset(box);
+	for (const WideRef &k : kids)
+		box_grow(box, k.box);
+	double extent = 0.0;
+	for (int a = 0; a < 3; a++) {
+		n.origin[a] = box.lo[a];
+		extent = std::max(extent, static_cast<double>(box.hi[a]) - static_cast<double>(box.lo[a]));
+	}
+	int e = -40;
+	if (extent > 0.0) {
+		int ex;
+		std::frexp(extent / (kWideGrid - 1.0), &ex); /* extent / 1022 = m * 2^ex, m in [0.5, 1) => 2^ex >= extent / 1022 */
+		e = std::min(std::max(ex, -40), 40);
+	}
+	double scale = std::ldexp(1.0, e);
+	/* a scale clamped from above cannot hold the node: widen until it does (boxes that large are not built in practice) */
+	while (extent > (kWideGrid - 1.0) * scale) {
+		e++;
+		scale = std::ldexp(1.0, e);
+	}
+	n.meta = (n.meta & ~0xffu) | static_cast<uint32_t>(e + 127);
+	const uint16_t empty_c = half_bits(0.f), empty_h = 0xfc00u; /* -infinity: the slab of an empty slot is inverted on every axis */
+	for (int a = 0; a < 3; a++)
+		for (int j = 0; j < 8; j++) {
+			n.plane[a][0][j] = empty_c;
+			n.plane[a][1][j] = empty_h;
+		}
+	for (size_t k = 0; k < kids.size(); k++) {
+		const int j = slot_of[k];
+		for (int a = 0; a < 3; a++) {
+			const double o = n.origin[a];
+			double lo = std::floor((static_cast<double>(kids[k].box.lo[a]) - o) / scale);
+			double hi = std::ceil((static_cast<double>(kids[k].box.hi[a]) - o) / scale);
+			lo = std::min(std::max(lo, 0.0), static_cast<double>(kWideGrid));
+			hi = std::min(std::max(hi, lo), static_cast<double>(kWideGrid));
+			const float c = static_cast<float>(0.5 * (lo + hi)), h = static_cast<float>(0.5 * (hi - lo)) + kWideSlack;
+			n.plane[a][0][j] = half_bits(c);
+			n.plane[a][1][j] = half_bits(h);
+		}
+	}
+}
+
+void emit_node(WideBuilder &W, int32_t binary, int32_t id, int32_t parent, uint32_t depth)
 {
 	W.out.max_depth = std::max(W.out.max_depth, depth);
-	const int32_t id = static_cast<int32_t>(W.out.nodes.size());
-	W.out.nodes.emplace_back();
 	std::vector<WideRef> kids;
-	if (W.optimal) {
-		const int k = W.split[8 * static_cast<size_t>(node)];
-		expand(W, node, 0, k, kids);
-		expand(W, node, 1, 8 - k, kids);
-	} else {
-		for (int c = 0; c < 2; c++) {
-			const WideRef r = make_ref(W, node, c);
-			if (!(r.ref < 0 && r.box.lo[0] >= 1e30f))
-				kids.push_back(r);
-		}
-		/* open the binary child with the largest surface that is too big for a wide leaf */
-		while (kids.size() < 8) {
-			int best = -1;
-			float best_area = -1.f;
-			for (size_t i = 0; i < kids.size(); i++)
-				if (kids[i].ref >= 0 && kids[i].count > W.merge_prims && half_area(kids[i].box) > best_area) {
-					best_area = half_area(kids[i].box);
-					best = static_cast<int>(i);
-				}
-			if (best < 0)
-				break;
-			const int32_t open = kids[best].ref;
-			kids[best] = make_ref(W, open, 0);
-			kids.push_back(make_ref(W, open, 1));
-		}
+	const int k = W.split[8 * static_cast<size_t>(binary)];
+	expand(W, binary, 0, k, kids);
+	expand(W, binary, 1, 8 - k, kids);
+	/* slots: leaves first, then inner children; each kind sorted along the longest axis of the node
+	 * (the closest-hit walk takes the slots of a kind in that order, or in reverse for a ray going the
+	 * other way, so that near children tend to come first) */
+	Aabb box;
+	box_reset(box);
+	for (const WideRef &r : kids)
+		box_grow(box, r.box);
+	int axis = 0;
+	for (int a = 1; a < 3; a++)
+		if (box.hi[a] - box.lo[a] > box.hi[axis] - box.lo[axis])
+			axis = a;
+	std::vector<int> idx(kids.size());
+	for (size_t i = 0; i < kids.size(); i++)
+		idx[i] = static_cast<int>(i);
+	std::stable_sort(idx.begin(), idx.end(), [&](int x, int y) {
+		const bool lx = kids[x].ref < 0, ly = kids[y].ref < 0;
+		if (lx != ly)
+			return lx;
+		return kids[x].box.lo[axis] + kids[x].box.hi[axis] < kids[y].box.lo[axis] + kids[y].box.hi[axis];
+	});
+	std::vector<WideRef> sorted(kids.size());
+	std::vector<int> slot_of(kids.size());
+	uint32_t leaves = 0;
+	for (size_t i = 0; i < kids.size(); i++) {
+		sorted[i] = kids[idx[i]];
+		slot_of[i] = static_cast<int>(i);
+		if (sorted[i].ref < 0)
+			leaves++;
 	}
-	/* experiment (CRT_WIDE_ORDER=area, off by default): children are pushed in slot order and
-	 * popped in reverse, so the largest boxes last = visited first, which finds an opaque
-	 * occluder sooner; any-hit results do not depend on the order */
-	if (W.order_by_area)
-		std::stable_sort(kids.begin(), kids.end(), [](const WideRef &a, const WideRef &b) { return half_area(a.box) < half_area(b.box); });
-	for (int j = 0; j < 8; j++) {
-		int32_t code = kWideEmpty;
-		Aabb box;
-		for (int k = 0; k < 3; k++)
-			box.lo[k] = box.hi[k] = 1e30f;
-		if (j < static_cast<int>(kids.size())) {
-			const WideRef &r = kids[j];
-			box = r.box;
-			if (r.ref < 0 || r.count <= W.merge_prims)
-				code = encode_leaf(r.first, r.count); /* a whole small subtree becomes one leaf */
-			else
-				code = wide_node(W, r.ref, depth + 1);
-		}
-		WideNode &n = W.out.nodes[id]; /* re-fetch: the vector may have grown */
-		n.a[j][0] = box.lo[0];
-		n.a[j][1] = box.lo[1];
-		n.a[j][2] = box.lo[2];
-		n.a[j][3] = box.hi[0];
-		n.b[j][0] = box.hi[1];
-		n.b[j][1] = box.hi[2];
-		std::memcpy(&n.b[j][2], &code, sizeof code);
-		n.b[j][3] = 0.f;
+	const uint32_t inner = static_cast<uint32_t>(sorted.size()) - leaves;
+	const int32_t first_child = static_cast<int32_t>(W.out.nodes.size());
+	W.out.nodes.resize(W.out.nodes.size() + inner);
+	WideNode n;
+	std::memset(&n, 0, sizeof n);
+	n.meta = (((1u << leaves) - 1u) << 8) | ((((1u << inner) - 1u) << leaves) << 16) | (static_cast<uint32_t>(axis) << 24);
+	n.child_base = first_child - static_cast<int32_t>(leaves);
+	n.prim_base = static_cast<int32_t>(W.next_prim);
+	n.parent = parent;
+	for (uint32_t j = 0; j < leaves; j++) {
+		const uint32_t first = static_cast<uint32_t>(~sorted[j].ref) >> kLeafCountBits;
+		W.out.order[W.next_prim++] = W.bvh.order[first];
+		W.out.cost += static_cast<double>(W.prim_cost) * half_area(sorted[j].box);
 	}
-	return id;
+	W.out.cost += half_area(box);
+	quantize_node(n, sorted, slot_of);
+	W.out.nodes[id] = n;
+	for (uint32_t j = 0; j < inner; j++)
+		emit_node(W, sorted[leaves + j].ref, first_child + static_cast<int32_t>(j), id, depth + 1);
 }
 
 } // namespace
 
-void build_wide(const BvhResult &bvh, WideResult &out, uint32_t merge_prims)
+void build_wide(const std::vector<Aabb> &boxes, const BvhResult &bvh, WideTree &out)
 {
 	out.nodes.clear();
+	out.order.clear();
 	out.max_depth = 0;
+	out.cost = 0.0;
 	if (bvh.nodes.empty())
 		return;
-	WideBuilder W{ bvh, out, {}, {}, std::min(merge_prims, kWideLeafPrims) };
-	W.first.assign(bvh.nodes.size(), 0);
-	W.count.assign(bvh.nodes.size(), 0);
-	ranges(W, 0);
-	const char *mode = std::getenv("CRT_WIDE_COLLAPSE"); /* "greedy": largest surface first (the round-1 trees) */
-	W.optimal = !(mode && !std::strcmp(mode, "greedy"));
-	if (const char *e = std::getenv("CRT_WIDE_ORDER"))
-		W.order_by_area = !std::strcmp(e, "area");
+	WideBuilder W{ bvh, out, {}, {} };
 	if (const char *e = std::getenv("CRT_WIDE_PRIM_COST"))
 		W.prim_cost = static_cast<float>(std::atof(e));
-	if (W.optimal)
-		plan_collapse(W);
-	out.nodes.reserve(bvh.nodes.size() / 2 + 1);
-	wide_node(W, 0, 1);
-}
-
-
-/* ---- quantisation of the 8-wide nodes ----------------------------------------- */
-
-namespace {
-
-/* smallest power of two s with extent <= 255 * s, as an IEEE exponent byte */
-uint32_t scale_exponent(float extent)
-{
-	if (!(extent > 0.f))
-		return 1u; /* 2^-126: all planes quantise to 0 */
-	int e;
-	std::frexp(extent / 255.f, &e); /* extent / 255 = m * 2^e, m in [0.5, 1) => 2^e >= extent / 255 */
-	const int biased = std::min(std::max(e + 127, 1), 254);
-	return static_cast<uint32_t>(biased);
-}
-
-float exponent_scale(uint32_t biased)
-{
-	const uint32_t bits = biased << 23;
-	float f;
-	std::memcpy(&f, &bits, 4);
-	return f;
-}
-
-} // namespace
-
-void quantize_wide(const WideResult &wide, std::vector<QuantNode> &out)
-{
-	out.resize(wide.nodes.size());
-	for (size_t n = 0; n < wide.nodes.size(); n++) {
-		const WideNode &w = wide.nodes[n];
-		QuantNode &qn = out[n];
-		std::memset(&qn, 0, sizeof qn);
-		float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
-		int32_t code[8];
-		float clo[8][3], chi[8][3];
-		for (int j = 0; j < 8; j++) {
-			std::memcpy(&code[j], &w.b[j][2], 4);
-			clo[j][0] = w.a[j][0]; clo[j][1] = w.a[j][1]; clo[j][2] = w.a[j][2];
-			chi[j][0] = w.a[j][3]; chi[j][1] = w.b[j][0]; chi[j][2] = w.b[j][1];
-			if (code[j] == kWideEmpty)
-				continue;
-			for (int k = 0; k < 3; k++) {
-				lo[k] = std::min(lo[k], clo[j][k]);
-				hi[k] = std::max(hi[k], chi[j][k]);
-			}
-		}
-		uint32_t ebits = 0;
-		float scale[3];
-		for (int k = 0; k < 3; k++) {
-			if (lo[k] > hi[k])
-				lo[k] = hi[k] = 0.f;
-			qn.origin[k] = lo[k];
-			uint32_t e = scale_exponent(hi[k] - lo[k]);
-			/* origin + 255 * scale must reach hi in FP32 arithmetic */
-			while (e < 254u && qn.origin[k] + 255.f * exponent_scale(e) < hi[k])
-				e++;
-			scale[k] = exponent_scale(e);
-			ebits |= e << (8 * k);
-		}
-		qn.exponents = ebits;
-		for (int j = 0; j < 8; j++) {
-			qn.code[j] = code[j];
-			for (int k = 0; k < 3; k++) {
-				uint8_t ql = 255, qh = 0; /* empty child: inverted, never hit */
-				if (code[j] != kWideEmpty) {
-					int a = static_cast<int>(std::floor((clo[j][k] - qn.origin[k]) / scale[k]));
-					a = std::min(std::max(a, 0), 255);
-					while (a > 0 && qn.origin[k] + static_cast<float>(a) * scale[k] > clo[j][k])
-						a--;
-					int b = static_cast<int>(std::ceil((chi[j][k] - qn.origin[k]) / scale[k]));
-					b = std::min(std::max(b, 0), 255);
-					while (b < 255 && qn.origin[k] + static_cast<float>(b) * scale[k] < chi[j][k])
-						b++;
-					ql = static_cast<uint8_t>(a);
-					qh = static_cast<uint8_t>(b);
-				}
-				qn.q[k][0][j] = ql;
-				qn.q[k][1][j] = qh;
-			}
-		}
-	}
+	plan_collapse(W);
+	out.order.assign(boxes.size(), 0);
+	out.nodes.reserve(bvh.nodes.size() / 3 + 1);
+	out.nodes.emplace_back();
+	emit_node(W, 0, 0, -1, 1);
+	const BvhNode &root = bvh.nodes[0];
+	Aabb rb;
+	box_reset(rb);
+	for (int c = 0; c < 2; c++)
+		if (!absent(child_box(root, c)))
+			box_grow(rb, child_box(root, c));
+	const float ra = half_area(rb);
+	out.cost = ra > 0.f ? out.cost / ra : 0.0;
 }
 
 } // namespace crt

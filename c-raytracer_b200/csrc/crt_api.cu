@@ -21,6 +21,9 @@ namespace {
 
 thread_local char g_error[512] = "";
 
+constexpr uint32_t kMaxBounces = 4096;       /* pending-ray stack depth is max_bounces + 4 per lane */
+constexpr uint32_t kMaxLights = 0x3fffffffu; /* light-sample indices and draw counters are 32-bit (2 draws per sample) */
+
 int fail(int code, const char *fmt, ...)
 {
 	va_list ap;
@@ -68,6 +71,10 @@ struct crt_scene {
 	crt_scene_info info{};
 	std::vector<void *> allocs;
 	std::vector<int32_t> slot_object; /* host copy: prim slot -> scene object (for the ray-batch seams) */
+	uint32_t num_materials = 0;
+	uint32_t wide_depth = 0;
+	uint32_t *deep = nullptr;  /* spill strips of the walk's inner stacks, only for trees deeper than kInnerStack */
+	size_t deep_words = 0;
 	/* per-frame scratch, grown on demand */
 	float *row_pos = nullptr;
 	size_t row_pos_floats = 0;
@@ -184,6 +191,7 @@ void crt_scene_destroy(crt_scene *s)
 		cudaFree(p);
 	cudaFree(s->row_pos);
 	cudaFree(s->pending);
+	cudaFree(s->deep);
 	cudaFree(s->tile_counter);
 	cudaFree(s->counters);
 	cudaFree(s->d_raster);
@@ -209,6 +217,7 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 
 	crt_scene *s = new crt_scene();
 	s->device = device;
+	s->num_materials = desc->num_materials;
 	cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
 
 	/* ---- materials ------------------------------------------------------ */
@@ -253,9 +262,14 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 				e.b = make_float4(o.b[0], o.b[1], o.b[2], 0.f);
 				e.c = make_float4(o.c[0], o.c[1], o.c[2], 0.f);
 			}
-			const float inv = 1.f / static_cast<float>(o.num_lights);
+			/* an emitter with no samples lights nothing: keep ke_n finite */
+			const float inv = o.num_lights ? 1.f / static_cast<float>(o.num_lights) : 0.f;
 			for (int k = 0; k < 3; k++)
 				e.ke_n[k] = m.ke[k] * inv;
+			if (static_cast<uint64_t>(total_lights) + o.num_lights > kMaxLights) {
+				delete s;
+				return fail(CRT_ERR_INVALID, "more than %u light samples in the scene", kMaxLights);
+			}
 			total_lights += o.num_lights;
 			emitters.push_back(e);
 		}
@@ -284,26 +298,22 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 	}
 	BvhResult bvh;
 	build_bvh(boxes, bvh);
-	/* the shadow walk's tree: 8-wide collapse of the binary tree, quantised child boxes */
-	WideResult wide;
-	uint32_t merge_prims = 0;
-	if (const char *e = std::getenv("CRT_WIDE_MERGE"))
-		merge_prims = static_cast<uint32_t>(std::max(0, std::atoi(e)));
-	build_wide(bvh, wide, merge_prims);
-	std::vector<QuantNode> qnodes;
-	quantize_wide(wide, qnodes);
-	if (bvh.max_depth + 1u > static_cast<uint32_t>(kStackSize) || 7u * wide.max_depth + 1u > static_cast<uint32_t>(kStackSize)) {
+	/* the device tree: 8-wide collapse of the binary tree, one primitive per leaf slot, half-precision child boxes */
+	WideTree wide;
+	build_wide(boxes, bvh, wide);
+	if (wide.max_depth > kWideMaxDepth || wide.nodes.size() > kWideMaxNodes || bounded.size() > kWideMaxPrims) {
 		delete s;
-		return fail(CRT_ERR_UNSUPPORTED, "BVH too deep for the device stacks (binary %u, wide %u levels)", bvh.max_depth, wide.max_depth);
+		return fail(CRT_ERR_UNSUPPORTED, "scene too large for the device tree (%zu nodes, %zu primitives, %u levels)",
+			wide.nodes.size(), bounded.size(), wide.max_depth);
 	}
 	s->info.build_ms = now_ms() - t0;
 
-	/* ---- primitive records in leaf order ---------------------------------- */
+	/* ---- primitive records in the order of the wide tree -------------------- */
 	const double t1 = now_ms();
-	std::vector<float4> prims(3 * bounded.size()), normals(bounded.size());
+	std::vector<float4> prims(4 * bounded.size());
 	s->slot_object.resize(bounded.size());
 	for (size_t slot = 0; slot < bounded.size(); slot++) {
-		const uint32_t oi = bounded[bvh.order[slot]];
+		const uint32_t oi = bounded[wide.order[slot]];
 		const crt_object &o = desc->objects[oi];
 		const crt_material &m = mats[o.material];
 		uint32_t info = static_cast<uint32_t>(o.material) | ((m.flags & CRT_MAT_TRANSPARENT) ? PRIM_TRANSPARENT : 0u);
@@ -311,30 +321,26 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 		s->slot_object[slot] = static_cast<int32_t>(oi);
 		if (o.type == CRT_OBJ_SPHERE) {
 			info |= PRIM_SPHERE;
-			prims[3 * slot + 0] = make_float4(o.a[0], o.a[1], o.a[2], o.epsilon);
-			prims[3 * slot + 1] = make_float4(o.b[0], 0.f, 0.f, as_float(info));
-			prims[3 * slot + 2] = make_float4(0.f, 0.f, 0.f, as_float(oi));
-			normals[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+			prims[4 * slot + 0] = make_float4(o.a[0], o.a[1], o.a[2], o.epsilon);
+			prims[4 * slot + 1] = make_float4(o.b[0], 0.f, 0.f, as_float(info));
+			prims[4 * slot + 2] = make_float4(0.f, 0.f, 0.f, as_float(oi));
+			prims[4 * slot + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
 		} else {
-			prims[3 * slot + 0] = make_float4(o.a[0], o.a[1], o.a[2], o.epsilon);
-			prims[3 * slot + 1] = make_float4(o.b[0], o.b[1], o.b[2], as_float(info));
-			prims[3 * slot + 2] = make_float4(o.c[0], o.c[1], o.c[2], as_float(oi));
-			normals[slot] = make_float4(o.n[0], o.n[1], o.n[2], 0.f);
+			prims[4 * slot + 0] = make_float4(o.a[0], o.a[1], o.a[2], o.epsilon);
+			prims[4 * slot + 1] = make_float4(o.b[0], o.b[1], o.b[2], as_float(info));
+			prims[4 * slot + 2] = make_float4(o.c[0], o.c[1], o.c[2], as_float(oi));
+			prims[4 * slot + 3] = make_float4(o.n[0], o.n[1], o.n[2], 0.f);
 		}
 	}
 
 	/* ---- upload -------------------------------------------------------------- */
-	std::vector<float4> nodes(4 * bvh.nodes.size());
-	if (!bvh.nodes.empty())
-		std::memcpy(nodes.data(), bvh.nodes.data(), bvh.nodes.size() * sizeof(BvhNode));
-	std::vector<float4> wide_nodes(static_cast<size_t>(kWideStride) * qnodes.size());
-	for (size_t i = 0; i < qnodes.size(); i++)
-		std::memcpy(wide_nodes.data() + kWideStride * i, &qnodes[i], sizeof(QuantNode));
-	rc = upload(s, nodes, &s->d.nodes);
+	std::vector<float4> wide_nodes(8 * wide.nodes.size());
+	if (!wide.nodes.empty())
+		std::memcpy(wide_nodes.data(), wide.nodes.data(), wide.nodes.size() * sizeof(WideNode));
+	rc = CRT_OK;
 	if (!rc) rc = upload(s, wide_nodes, &s->d.wide);
 	s->wide_bytes = wide_nodes.size() * sizeof(float4);
 	if (!rc) rc = upload(s, prims, &s->d.prims);
-	if (!rc) rc = upload(s, normals, &s->d.normals);
 	if (!rc) rc = upload(s, planes, &s->d.planes);
 	if (!rc) rc = upload(s, obj_slot, &s->d.obj_slot);
 	if (!rc) rc = upload(s, emitters, &s->d.emitters);
@@ -349,7 +355,8 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 		crt_scene_destroy(s);
 		return rc;
 	}
-	s->d.num_nodes = static_cast<uint32_t>(bvh.nodes.size());
+	s->d.num_nodes = static_cast<uint32_t>(wide.nodes.size());
+	s->wide_depth = wide.max_depth;
 	s->d.num_prims = static_cast<uint32_t>(bounded.size());
 	s->d.num_planes = static_cast<uint32_t>(planes.size() / 2);
 	s->d.num_emitters = static_cast<uint32_t>(emitters.size());
@@ -363,7 +370,7 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 	s->info.num_emitters = s->d.num_emitters;
 	s->info.total_lights = total_lights;
 	s->info.num_nodes = s->d.num_nodes;
-	s->info.max_depth = bvh.max_depth;
+	s->info.max_depth = wide.max_depth;
 	s->info.device = static_cast<uint32_t>(device);
 	s->info.sm_count = static_cast<uint32_t>(s->sm_count);
 	*out = s;
@@ -388,6 +395,12 @@ int crt_render_device(crt_scene *s, const crt_render_opts *opts, float *d_raster
 		return fail(CRT_ERR_INVALID, "bad shard %u of %u", opts->shard_index, opts->shard_count);
 	if (opts->gi_model == CRT_GI_PATH && opts->samples_per_pixel > 0x7fffffffu)
 		return fail(CRT_ERR_INVALID, "too many samples per pixel");
+	if (opts->max_bounces > kMaxBounces)
+		return fail(CRT_ERR_INVALID, "max_bounces %u exceeds the supported %u", opts->max_bounces, kMaxBounces);
+	/* the per-frame scratch (work counter, pending stacks, contribution slots, events) belongs to
+	 * the scene: one frame in flight per crt_scene */
+	if (s->frame_pending)
+		return fail(CRT_ERR_INVALID, "a frame of this scene is still in flight: call crt_render_device_sync() first");
 	CUDA_TRY(cudaSetDevice(s->device));
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
 	const size_t pixels = static_cast<size_t>(opts->width) * opts->height;
@@ -416,6 +429,19 @@ int crt_render_device(crt_scene *s, const crt_render_opts *opts, float *d_raster
 		s->pending_floats = 0;
 		CUDA_TRY(cudaMalloc(&s->pending, pending_floats * sizeof(float)));
 		s->pending_floats = pending_floats;
+	}
+
+	if (s->wide_depth > static_cast<uint32_t>(kInnerStack)) {
+		p.deep_depth = s->wide_depth - kInnerStack;
+		const size_t words = static_cast<size_t>(grid) * kWarpsPerBlock * p.deep_depth * 32;
+		if (s->deep_words < words) {
+			cudaFree(s->deep);
+			s->deep = nullptr;
+			s->deep_words = 0;
+			CUDA_TRY(cudaMalloc(&s->deep, words * sizeof(uint32_t)));
+			s->deep_words = words;
+		}
+		p.deep = s->deep;
 	}
 
 	p.sc = s->d;
@@ -616,8 +642,8 @@ int crt_texture_eval(crt_scene *s, int32_t material, const float *points, size_t
 {
 	if (!s || (n && (!points || !colors)))
 		return fail(CRT_ERR_INVALID, "NULL argument");
-	if (material < 0)
-		return fail(CRT_ERR_INVALID, "bad material index %d", material);
+	if (material < 0 || static_cast<uint32_t>(material) >= s->num_materials)
+		return fail(CRT_ERR_INVALID, "bad material index %d (scene has %u materials)", material, s->num_materials);
 	CUDA_TRY(cudaSetDevice(s->device));
 	DeviceBuffer d_p, d_c;
 	CUDA_TRY(d_p.alloc(n * 3 * sizeof(float)));

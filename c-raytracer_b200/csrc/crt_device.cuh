@@ -5,13 +5,13 @@
  *
  * Device layout (all arrays in HBM, read through the read-only path; the
  * working set of every configuration fits the 126 MB L2):
- *   nodes   : BvhNode[ ], 64 B, four float4 loads per visit (bvh_build.h)
- *   prims   : 3 x float4 per bounded primitive, in BVH leaf order ("slot")
- *               triangle: (v0.xyz, eps) (e0.xyz, info) (e1.xyz, object)
- *               sphere  : (c.xyz,  eps) (r, 0, 0, info) (0, 0, 0, object)
+ *   wide    : WideNode[ ], 128 B, four 256-bit loads per visit (bvh_build.h)
+ *   prims   : 4 x float4 (64 B) per bounded primitive, in the order of the wide tree ("slot")
+ *               triangle: (v0.xyz, eps) (e0.xyz, info) (e1.xyz, object) (unit normal, 0)
+ *               sphere  : (c.xyz,  eps) (r, 0, 0, info) (0, 0, 0, object) (0, 0, 0, 0)
  *             info = material index | PRIM_TRANSPARENT | PRIM_SPHERE,
- *             object = scene-order object index (both as raw int bits)
- *   normals : float4 per slot, unit triangle normal (closest-hit shading only)
+ *             object = scene-order object index (both as raw int bits);
+ *             the normal is read by closest-hit shading only
  *   planes  : 2 x float4 per plane: (n.xyz, d) (eps, info, object, 0)
  *   obj_slot: int per scene object: slot >= 0, or ~plane_index
  *   emitters: DEmitter per emitter, scene order
@@ -22,6 +22,7 @@
 
 #include <cfloat>
 #include <cstdint>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include "crt.h"
@@ -33,13 +34,9 @@ constexpr uint32_t PRIM_SPHERE = 0x80000000u;
 constexpr uint32_t PRIM_TRANSPARENT = 0x40000000u;
 constexpr uint32_t PRIM_MATERIAL_MASK = 0x00ffffffu;
 
-constexpr int kStackSize = 128;         /* >= binary tree depth (closest hit) and 7 * wide tree depth + 1 (shadow walk): checked at scene creation */
-constexpr int kStackSentinel = 0x7fffffff;
-constexpr int kLeafBits = 3;
-#ifndef CRT_WIDE_NODE_STRIDE
-#define CRT_WIDE_NODE_STRIDE 6             /* float4 per quantised node in memory: 6 = packed (96 B), 8 = one 128-byte line each */
-#endif
-constexpr int kWideStride = CRT_WIDE_NODE_STRIDE;
+constexpr float kWideGridF = 1023.f;     /* bvh_build.h kWideGrid */
+constexpr float kWideTauScale = 2048.f;  /* half-precision crossings are in units of 2048 grid steps: the cube spans [0, 1/2] */
+constexpr float kWideSlopeMax = 48.f;    /* clamp of |idir| / 2048: beyond it the ray moves < 1/48 unit inside the cube; h |i| <= 516 * 48 stays finite */
 constexpr float kPi = 3.1415927f;       /* reference src/core/type.h:30 */
 
 struct DEmitter {
@@ -55,10 +52,8 @@ struct DEmitter {
 };
 
 struct DScene {
-	const float4 *nodes;
-	const float4 *wide;  /* quantised 8-wide nodes of the shadow walk, 6 float4 each (bvh_build.h QuantNode) */
+	const float4 *wide;  /* 8-wide nodes, 8 float4 each (bvh_build.h WideNode) */
 	const float4 *prims;
-	const float4 *normals;
 	const float4 *planes;
 	const int32_t *obj_slot;
 	const DEmitter *emitters;
@@ -197,9 +192,8 @@ __device__ __forceinline__ bool hit_plane(const float4 pl, const float eps, cons
 template <bool COUNT>
 __device__ __forceinline__ bool hit_prim(const DScene &sc, int slot, const Ray &r, float &t, uint32_t &info, int &object, Counters &cn)
 {
-	const float4 p0 = ldg4(sc.prims + 3 * slot);
-	const float4 p1 = ldg4(sc.prims + 3 * slot + 1);
-	const float4 p2 = ldg4(sc.prims + 3 * slot + 2);
+	const float4 *rec = sc.prims + 4 * (size_t)slot;
+	const float4 p0 = ldg4(rec), p1 = ldg4(rec + 1), p2 = ldg4(rec + 2);
 	info = __float_as_uint(p1.w);
 	object = __float_as_int(p2.w);
 	if (info & PRIM_SPHERE)
@@ -207,46 +201,155 @@ __device__ __forceinline__ bool hit_prim(const DScene &sc, int slot, const Ray &
 	return hit_triangle<COUNT>(p0, p1, p2, r, t, cn);
 }
 
-/* ---- BVH traversal --------------------------------------------------------- */
+/* ---- BVH traversal ---------------------------------------------------------
+ *
+ * Both walks (closest hit and the any-hit shadow query) read the same tree: 8-wide
+ * nodes of 128 bytes (bvh_build.h WideNode), four 256-bit loads per visit.  A node
+ * visit tests its eight child boxes in HALF2 arithmetic, two children per
+ * instruction:
+ *
+ *   - the ray is first clipped, in FP32, against the node's grid cube [0, 1023]^3
+ *     and re-based to its entry point p (so every quantity of the child test is at
+ *     most ~1023 grid units, where half precision resolves 1/2 unit), with the ray
+ *     parameter rescaled so that the dominant axis advances one grid unit per unit
+ *     (tau' in [0, 1023] inside the cube);
+ *   - per axis and child pair, with tau'' = tau' / 2048 (the cube spans [0, 1/2]):
+ *       a = c - p;  q = a * i;  tn = q - h |i|;  tf = q + h |i|
+ *     (HADD2, HMUL2, two HFMA2; i = idir / 2048 clamped to |i| <= 48), c = box
+ *     centre, h = half extent padded by kWideSlack = 3.5 grid units, which bounds
+ *     every rounding above: 1/4 unit for p, 1/4 for c - p, 2^-10 relative for the
+ *     product and the FMA on magnitudes <= 1535 units, leaving 3/4 unit for the FP32
+ *     clip.  With the clamp no product overflows (|a i| <= 1100 * 48, h |i| <= 516 * 48),
+ *     so tn / tf are finite or a correctly signed infinity, never inf - inf; a slope
+ *     beyond the clamp moves the ray by less than 1/48 of a unit inside the cube,
+ *     far inside the slack, so evaluating it with the clamped slope stays
+ *     conservative.  When the FP32 clip itself cannot guarantee its 3/4 unit
+ *     (origins ~10^6 grid units from the node) the visit reports every child as
+ *     hit -- slower, never wrong;
+ *   - tmin = max(tn.x, tn.y, tn.z, 0), tmax = min(tf.x, tf.y, tf.z, limit) with the
+ *     three-input half2 min/max, one HSET2 per child pair.
+ *
+ * A visit yields an 8-bit mask of hit slots; leaf slots and inner slots are
+ * contiguous in primitive / node index (bvh_build.h), so the walk state is a pair
+ * of (base << 8 | mask) words per kind and a short stack of such words. */
 
-struct RayBox {
-	float idx, idy, idz; /* 1 / d */
-	float ox, oy, oz;    /* o / d, so that t = plane * id - o */
+constexpr int kInnerStack = 12;  /* inner-group entries per lane kept in shared memory; deeper ones spill (DeepStack) */
+constexpr int kLeafStack = 8;    /* leaf-group entries per lane ([slot][lane]); a node visit adds at most one */
+constexpr int kDeepStack = 64;   /* >= kWideMaxDepth */
+
+/* ray constants of the wide walk (beside the ray itself) */
+struct WideRay {
+	float inx, iny, inz;    /* maxd / d: grid units of the dominant axis per grid unit of this axis (|.| >= 1) */
+	float maxd, inv_maxd;   /* max |d| and its reciprocal: tau = t * maxd / scale */
+	uint32_t hx, hy, hz;    /* half2 (i, i) of (maxd / d) / 2048, clamped to +-kWideSlopeMax */
 };
 
-__device__ __forceinline__ RayBox make_raybox(const Ray &r)
+__device__ __forceinline__ uint32_t h2_bits(__half2 v) { return *reinterpret_cast<uint32_t *>(&v); }
+__device__ __forceinline__ __half2 h2_from(uint32_t v) { return *reinterpret_cast<__half2 *>(&v); }
+
+__device__ __forceinline__ uint32_t pack_half2(float lo, float hi)
 {
-	RayBox b;
-	b.idx = 1.f / r.dx;
-	b.idy = 1.f / r.dy;
-	b.idz = 1.f / r.dz;
-	b.ox = r.ox * b.idx;
-	b.oy = r.oy * b.idy;
-	b.oz = r.oz * b.idz;
-	return b;
+	return h2_bits(__floats2half2_rn(lo, hi));
 }
 
-/* Slab test of both child boxes of a node against [0, tlimit].
- * fminf/fmaxf drop NaNs (0 * inf for an axis-parallel ray starting on a slab
- * plane), which keeps the interval -- the reference's comparisons behave the
- * same way (accel.c:112-158).  The reference's extra `tmax > node epsilon`
- * cull is deliberately not reproduced. */
-__device__ __forceinline__ void test_children(const float4 xy0, const float4 xy1, const float4 z01, const Ray &r,
-	const RayBox &rb, float tlimit, bool &hit0, bool &hit1, float &tmin0, float &tmin1)
+__device__ __forceinline__ float safe_idir(float d, float maxd)
 {
-	/* (plane - o) * id, written as in the reference so grazing cases round alike */
-	const float c0lox = (xy0.x - r.ox) * rb.idx, c0hix = (xy0.y - r.ox) * rb.idx;
-	const float c0loy = (xy0.z - r.oy) * rb.idy, c0hiy = (xy0.w - r.oy) * rb.idy;
-	const float c0loz = (z01.x - r.oz) * rb.idz, c0hiz = (z01.y - r.oz) * rb.idz;
-	const float c1lox = (xy1.x - r.ox) * rb.idx, c1hix = (xy1.y - r.ox) * rb.idx;
-	const float c1loy = (xy1.z - r.oy) * rb.idy, c1hiy = (xy1.w - r.oy) * rb.idy;
-	const float c1loz = (z01.z - r.oz) * rb.idz, c1hiz = (z01.w - r.oz) * rb.idz;
-	tmin0 = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), 0.f));
-	const float tmax0 = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), tlimit));
-	tmin1 = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), 0.f));
-	const float tmax1 = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), tlimit));
-	hit0 = tmin0 <= tmax0;
-	hit1 = tmin1 <= tmax1;
+	/* maxd / d with a floor on |d|: finite everywhere, huge for an axis the ray is parallel to */
+	const float a = fabsf(d) > 1e-18f ? d : copysignf(1e-18f, d);
+	return maxd / a;
+}
+
+__device__ __forceinline__ WideRay make_wide_ray(const Ray &r)
+{
+	WideRay w;
+	w.maxd = fmaxf(fmaxf(fabsf(r.dx), fabsf(r.dy)), fabsf(r.dz));
+	w.inv_maxd = 1.f / w.maxd;
+	w.inx = safe_idir(r.dx, w.maxd);
+	w.iny = safe_idir(r.dy, w.maxd);
+	w.inz = safe_idir(r.dz, w.maxd);
+	const float big = kWideSlopeMax, sc = 1.f / kWideTauScale;
+	const float cx = fminf(fmaxf(w.inx * sc, -big), big), cy = fminf(fmaxf(w.iny * sc, -big), big), cz = fminf(fmaxf(w.inz * sc, -big), big);
+	w.hx = pack_half2(cx, cx); w.hy = pack_half2(cy, cy); w.hz = pack_half2(cz, cz);
+	return w;
+}
+
+struct alignas(32) Vec8 {
+	uint32_t v[8];
+};
+
+__device__ __forceinline__ Vec8 ldg8(const float4 *p)
+{
+	Vec8 r; /* one 256-bit load through the read-only path (LDG.E.ENL2.256.CONSTANT) */
+	asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+		: "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
+		: "l"(p));
+	return r;
+}
+
+struct WideHits {
+	uint32_t inner; /* (child_base << 8) | mask of hit inner slots */
+	uint32_t leaf;  /* (prim_base << 8) | mask of hit leaf slots */
+};
+
+/* One visit of wide node `node`: which of its children may the segment [0, limit] of the ray meet? */
+template <bool COUNT>
+__device__ __forceinline__ WideHits wide_node_test(const DScene &sc, const Ray &r, const WideRay &w, float limit, int node, Counters &cn)
+{
+	const float4 *n = sc.wide + 8 * (size_t)node;
+	const Vec8 head = ldg8(n), vx = ldg8(n + 2), vy = ldg8(n + 4), vz = ldg8(n + 6);
+	const uint32_t meta = head.v[3];
+	const float inv_s = __uint_as_float((254u - (meta & 0xffu)) << 23); /* 1 / scale, exact */
+	/* ray in grid coordinates, clipped against the grid cube */
+	const float olx = (r.ox - __uint_as_float(head.v[0])) * inv_s;
+	const float oly = (r.oy - __uint_as_float(head.v[1])) * inv_s;
+	const float olz = (r.oz - __uint_as_float(head.v[2])) * inv_s;
+	const float ax = -olx * w.inx, ay = -oly * w.iny, az = -olz * w.inz;                 /* tau of the planes g = 0 */
+	const float bx = fmaf(kWideGridF, w.inx, ax), by = fmaf(kWideGridF, w.iny, ay), bz = fmaf(kWideGridF, w.inz, az); /* g = 1023 */
+	float tin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));
+	const float tout = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+	tin = fminf(tin, 1e30f);
+	const float tind = tin * w.inv_maxd;
+	const float px = fmaf(tind, r.dx, olx), py = fmaf(tind, r.dy, oly), pz = fmaf(tind, r.dz, olz);
+	const float lim = fmaf(limit * w.maxd, inv_s, -tin); /* the ray's limit in tau', relative to the entry point */
+	/* FP32 error of p and lim: a few ulp of the magnitudes they were formed from */
+	const float mag = (fabsf(olx) + fabsf(oly)) + (fabsf(olz) + tin);
+	const uint32_t p2x = pack_half2(px, px), p2y = pack_half2(py, py), p2z = pack_half2(pz, pz);
+	/* + 2^-8 relative + 1 unit: above the true limit after the conversion (an overflow becomes +infinity) */
+	const float lim_up = fmaf(fabsf(lim), 0.00390625f, lim + 1.f) * (1.f / kWideTauScale);
+	const uint32_t l2 = pack_half2(lim_up, lim_up);
+	uint32_t hit = 0;
+	const __half2 nax = h2_from(w.hx | 0x80008000u), nay = h2_from(w.hy | 0x80008000u), naz = h2_from(w.hz | 0x80008000u); /* -|idir| */
+#pragma unroll
+	for (int k = 0; k < 4; k++) {
+		const __half2 cx = h2_from(vx.v[k]), hx = h2_from(vx.v[4 + k]);
+		const __half2 cy = h2_from(vy.v[k]), hy = h2_from(vy.v[4 + k]);
+		const __half2 cz = h2_from(vz.v[k]), hz = h2_from(vz.v[4 + k]);
+		const __half2 qx = __hmul2(__hsub2(cx, h2_from(p2x)), h2_from(w.hx));
+		const __half2 qy = __hmul2(__hsub2(cy, h2_from(p2y)), h2_from(w.hy));
+		const __half2 qz = __hmul2(__hsub2(cz, h2_from(p2z)), h2_from(w.hz));
+		const __half2 tnx = __hfma2(hx, nax, qx), tfx = __hfma2(hx, __hneg2(nax), qx);
+		const __half2 tny = __hfma2(hy, nay, qy), tfy = __hfma2(hy, __hneg2(nay), qy);
+		const __half2 tnz = __hfma2(hz, naz, qz), tfz = __hfma2(hz, __hneg2(naz), qz);
+		const __half2 tmin = __hmax2(__hmax2(__hmax2(tnx, tny), tnz), h2_from(0u));
+		const __half2 tmax = __hmin2(__hmin2(__hmin2(tfx, tfy), tfz), h2_from(l2));
+		const uint32_t m = __hle2_mask(tmin, tmax);
+		hit |= m & (0x00020001u << (2 * k)); /* slot 2k -> bit 2k, slot 2k + 1 -> bit 17 + 2k */
+	}
+	hit = (hit | (hit >> 16)) & 0xffu;
+	const uint32_t valid = ((meta >> 8) | (meta >> 16)) & 0xffu;
+	/* precision guard: beyond ~10^6 grid units the clip cannot place p to a fraction of a unit */
+	if (!(mag <= 1048576.f))
+		hit = valid;
+	/* the ray misses the grid cube (the parent's test is conservative), or the cube lies beyond the limit */
+	if (tin > fmaf(fabsf(tout) + tin, 1e-6f, tout) || lim < -1.f - mag * 1e-6f)
+		hit = 0;
+	hit &= valid;
+	if (COUNT)
+		cn.box += (uint32_t)__popc(valid);
+	WideHits res;
+	res.leaf = ((uint32_t)head.v[5] << 8) | (hit & (meta >> 8) & 0xffu);
+	res.inner = ((uint32_t)head.v[4] << 8) | (hit & (meta >> 16) & 0xffu);
+	return res;
 }
 
 struct Hit {
@@ -255,13 +358,25 @@ struct Hit {
 	int slot;   /* prim slot, or ~plane index */
 };
 
+/* lowest set bit of the 8-bit mask of a group word, removed from it */
+__device__ __forceinline__ int group_take(uint32_t &g)
+{
+	const int j = __ffs((int)(g & 0xffu)) - 1;
+	g &= g - 1u;
+	return j;
+}
+
+__device__ __forceinline__ int group_base(uint32_t g) { return (int)g >> 8; }
+
 /* Nearest hit over planes then the BVH: get_closest_intersection()
  * (reference render.c:118-124, object.c:168-181, accel.c:322-353).
  * Strict '<' like the reference; on an exact tie between bounded primitives
  * the lower scene index wins (the reference's winner depends on its Morton
- * order). */
-template <bool COUNT>
-__device__ __forceinline__ Hit trace_closest(const DScene &sc, const Ray &r, int *stack, Counters &cn)
+ * order).  Depth-first over the wide tree with the current nearest
+ * distance as the limit of every node test; the primitives of a node are tested
+ * before its inner children are entered. */
+template <bool COUNT, class STACKS>
+__device__ __forceinline__ Hit trace_closest(const DScene &sc, const Ray &r, const STACKS &st, Counters &cn)
 {
 	Hit best;
 	best.t = FLT_MAX;
@@ -280,48 +395,33 @@ __device__ __forceinline__ Hit trace_closest(const DScene &sc, const Ray &r, int
 	if (sc.num_nodes == 0)
 		return best;
 
-	const RayBox rb = make_raybox(r);
-	int sp = 0;
-	stack[sp++] = kStackSentinel;
-	int node = 0;
+	const WideRay w = make_wide_ray(r);
 	bool bounded_found = false;
-	while (node != kStackSentinel) {
-		while (node >= 0 && node != kStackSentinel) {
-			const float4 *n = sc.nodes + 4 * node;
-			const float4 xy0 = ldg4(n), xy1 = ldg4(n + 1), z01 = ldg4(n + 2);
-			const float4 ch = ldg4(n + 3);
-			bool h0, h1;
-			float t0, t1;
-			test_children(xy0, xy1, z01, r, rb, best.t, h0, h1, t0, t1);
-			Cnt<COUNT>::add(cn.box, 2u);
-			const int c0 = __float_as_int(ch.x), c1 = __float_as_int(ch.y);
-			if (!h0 && !h1) {
-				node = stack[--sp];
-			} else if (h0 && h1) {
-				const bool swap = t1 < t0;
-				node = swap ? c1 : c0;
-				stack[sp++] = swap ? c0 : c1;
-			} else {
-				node = h0 ? c0 : c1;
-			}
-		}
-		if (node < 0) {
-			const int leaf = ~node;
-			const int first = leaf >> kLeafBits, count = (leaf & ((1 << kLeafBits) - 1)) + 1;
-			for (int i = 0; i < count; i++) {
-				float t;
-				uint32_t info;
-				int object;
-				if (hit_prim<COUNT>(sc, first + i, r, t, info, object, cn)) {
-					if (t < best.t || (t == best.t && bounded_found && object < best.object)) {
-						best.t = t;
-						best.object = object;
-						best.slot = first + i;
-						bounded_found = true;
-					}
+	int sp = 0;
+	uint32_t cur = 1u; /* group (base 0, slot 0): the root */
+	while (cur & 0xffu) {
+		const int node = group_base(cur) + group_take(cur);
+		WideHits h = wide_node_test<COUNT>(sc, r, w, fminf(best.t, 1e30f), node, cn);
+		while (h.leaf & 0xffu) {
+			const int slot = group_base(h.leaf) + group_take(h.leaf);
+			float t;
+			uint32_t info;
+			int object;
+			if (hit_prim<COUNT>(sc, slot, r, t, info, object, cn)) {
+				if (t < best.t || (t == best.t && bounded_found && object < best.object)) {
+					best.t = t;
+					best.object = object;
+					best.slot = slot;
+					bounded_found = true;
 				}
 			}
-			node = stack[--sp];
+		}
+		if (h.inner & 0xffu) {
+			if (cur & 0xffu)
+				st.put_inner(sp++, cur);
+			cur = h.inner;
+		} else if (!(cur & 0xffu) && sp > 0) {
+			cur = st.get_inner(--sp);
 		}
 	}
 	return best;
@@ -334,7 +434,7 @@ __device__ __forceinline__ Hit trace_closest(const DScene &sc, const Ray &r, int
  * (accel.c:367).  It runs in resumable pieces, so that the render kernel's
  * lanes can be refilled and scheduled step by step:
  * shadow_planes() is the linear plane scan, the ShadowWalk steps below walk
- * the quantised 8-wide tree; trace_shadow_wide() strings them together for
+ * the wide tree; trace_shadow_wide() strings them together for
  * one ray per thread (the crt_trace_shadow seam). */
 template <bool COUNT>
 __device__ __forceinline__ bool shadow_planes(const DScene &sc, const Ray &r, float dist, float &lr, float &lg, float &lb, Counters &cn)
@@ -358,183 +458,123 @@ __device__ __forceinline__ bool shadow_planes(const DScene &sc, const Ray &r, fl
 
 /* Any-hit order is free (every occluder within dist counts, accel.c:360-387),
  * so the walk is split into two kinds of unit steps that a lane can take in
- * any interleaving: an INNER step (one node: two slab tests, hit leaves go to
- * the lane's leaf queue, hit inner children to its stack) and a PRIM step (one
- * primitive of the queued leaves).  The render kernel lets the warp vote each
- * iteration for the kind more lanes are ready for, instead of a while-while
- * loop in which lanes at a leaf wait for the longest descent of the warp. */
-constexpr int kLeafQueue = 16; /* queued leaf codes per lane ([slot][lane]); a node step adds up to 8 */
-
+ * any interleaving: a NODE step (one wide node: eight slab tests; the hit leaf
+ * slots become one leaf group, the hit inner slots one inner group) and a PRIM
+ * step (one primitive of the current leaf group).  The render kernel lets the
+ * warp vote each iteration for the kind more lanes are ready for, instead of a
+ * while-while loop in which lanes at a leaf wait for the longest descent of the
+ * warp.  The current group of each kind lives in a register; only a group that
+ * is superseded while slots remain goes to the lane's stack of that kind. */
 struct ShadowWalk {
-	int node;       /* wide node to visit next, kStackSentinel: none */
-	int top;        /* top of the stack, kept in a register: a pop's load is only needed by the NEXT pop */
-	int sp;         /* entries in stack[] below top */
-	int leaf_first; /* primitive slot being tested next */
-	int leaf_left;  /* primitives left in the current leaf */
-	int qhead, qcount;
+	uint32_t inner; /* current inner group, mask 0: none */
+	uint32_t leaf;  /* current leaf group, mask 0: none */
+	int isp, lsp;   /* entries on the inner / leaf stack */
 };
 
 __device__ __forceinline__ void shadow_walk_reset(ShadowWalk &w)
 {
-	w.node = kStackSentinel;
-	w.top = kStackSentinel;
-	w.sp = 0;
-	w.leaf_first = 0;
-	w.leaf_left = 0;
-	w.qhead = 0;
-	w.qcount = 0;
+	w.inner = 0;
+	w.leaf = 0;
+	w.isp = 0;
+	w.lsp = 0;
 }
 
 __device__ __forceinline__ bool shadow_walk_busy(const ShadowWalk &w)
 {
-	return w.node != kStackSentinel || w.leaf_left > 0 || w.qcount > 0;
+	return ((w.inner | w.leaf) & 0xffu) != 0u;
 }
 
 __device__ __forceinline__ bool shadow_can_inner(const ShadowWalk &w)
 {
-	return w.node != kStackSentinel && w.qcount <= kLeafQueue - 8;
+	return (w.inner & 0xffu) != 0u && w.lsp < kLeafStack;
 }
 
 __device__ __forceinline__ bool shadow_can_prim(const ShadowWalk &w)
 {
-	return w.leaf_left > 0 || w.qcount > 0;
+	return (w.leaf & 0xffu) != 0u;
 }
 
-/* The per-ray leaf queue, kLeafQueue entries.  In the render kernel it lives in
- * shared memory as [slot][lane]; the lane's base is kept as a 32-bit shared
- * address in a register the compiler cannot rematerialise (re-deriving it from
- * %tid at every push cost 15 instructions, a fifth of the node step).  The
- * one-ray-per-thread seam kernel uses a private array. */
-struct SharedLeafQueue {
-	uint32_t base; /* shared-space byte address of slot 0 of this lane */
-	__device__ __forceinline__ explicit SharedLeafQueue(const int *lane_slot0)
+/* The lane's two stacks.  In the render kernel they live in shared memory as
+ * [slot][lane] words; the lane's base is kept as a 32-bit shared address in a
+ * register the compiler cannot rematerialise (re-deriving it from %tid at every
+ * push cost 15 instructions).  Inner entries beyond kInnerStack (trees deeper than
+ * that are rare) spill to a per-lane strip of global scratch.  The
+ * one-ray-per-thread seam kernels use private arrays. */
+struct SharedStacks {
+	uint32_t base;  /* shared-space byte address of inner slot 0 of this lane; leaf slots follow the inner ones */
+	uint32_t *deep; /* this lane's spill strip (stride 32 words), may be null when the tree is shallow */
+	__device__ __forceinline__ SharedStacks(const uint32_t *lane_slot0, uint32_t *deep_strip) : deep(deep_strip)
 	{
 		uint32_t b = static_cast<uint32_t>(__cvta_generic_to_shared(lane_slot0));
 		asm volatile("mov.u32 %0, %1;" : "=r"(base) : "r"(b));
 	}
-	__device__ __forceinline__ void put(int slot, int v) const
+	__device__ __forceinline__ void put_inner(int slot, uint32_t v) const
 	{
-		asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + (uint32_t)slot * 128u), "r"(v) : "memory");
+		if (slot < kInnerStack)
+			asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + (uint32_t)slot * 128u), "r"(v) : "memory");
+		else
+			deep[(slot - kInnerStack) * 32] = v;
 	}
-	__device__ __forceinline__ int get(int slot) const
+	__device__ __forceinline__ uint32_t get_inner(int slot) const
 	{
-		int v;
-		asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + (uint32_t)slot * 128u) : "memory");
+		uint32_t v;
+		if (slot < kInnerStack)
+			asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + (uint32_t)slot * 128u) : "memory");
+		else
+			v = deep[(slot - kInnerStack) * 32];
+		return v;
+	}
+	__device__ __forceinline__ void put_leaf(int slot, uint32_t v) const
+	{
+		asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + (uint32_t)(kInnerStack + slot) * 128u), "r"(v) : "memory");
+	}
+	__device__ __forceinline__ uint32_t get_leaf(int slot) const
+	{
+		uint32_t v;
+		asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + (uint32_t)(kInnerStack + slot) * 128u) : "memory");
 		return v;
 	}
 };
 
-struct PrivateLeafQueue {
-	int *slots;
-	__device__ __forceinline__ void put(int slot, int v) const { slots[slot] = v; }
-	__device__ __forceinline__ int get(int slot) const { return slots[slot]; }
+struct PrivateStacks {
+	uint32_t *inner, *leaf;
+	__device__ __forceinline__ void put_inner(int slot, uint32_t v) const { inner[slot] = v; }
+	__device__ __forceinline__ uint32_t get_inner(int slot) const { return inner[slot]; }
+	__device__ __forceinline__ void put_leaf(int slot, uint32_t v) const { leaf[slot] = v; }
+	__device__ __forceinline__ uint32_t get_leaf(int slot) const { return leaf[slot]; }
 };
 
-/* 1/d with a floor on |d|: keeps the quantised slab arithmetic finite (no 0 * inf) and
- * still puts both planes of an axis at -+huge for an axis-parallel ray */
-__device__ __forceinline__ float safe_rcp(float d)
+template <bool COUNT, class STACKS>
+__device__ __forceinline__ void shadow_inner_step(const DScene &sc, const Ray &r, const WideRay &rw, float dist, ShadowWalk &w,
+	const STACKS &st, Counters &cn)
 {
-	return 1.f / (fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d));
-}
-
-/* ray constants of the wide walk: idir, and per-axis byte selectors are derived per node */
-struct RayWide {
-	float idx, idy, idz;
-};
-
-/* 2^23 + byte k of word, without a conversion instruction: the byte goes into the mantissa of 2^23 */
-__device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t selector)
-{
-	return __uint_as_float(__byte_perm(word, 0x4b000000u, selector));
-}
-
-constexpr float kSlabUlps = 9.5367431640625e-7f; /* 16 * 2^-24 */
-
-/* One visit of a quantised 8-wide node (bvh_build.h QuantNode): six vector loads,
- * eight slab tests; the child pushes are predicated, not branched (lanes hit
- * different children). */
-template <bool COUNT, class QUEUE>
-__device__ __forceinline__ void shadow_inner_step(const DScene &sc, const Ray &r, const RayWide &rw, float dist, ShadowWalk &w,
-	int *stack, const QUEUE &q, Counters &cn)
-{
-	const float4 *n = sc.wide + kWideStride * (size_t)w.node;
-	const float4 w0 = ldg4(n), w1 = ldg4(n + 1), w2 = ldg4(n + 2), w3 = ldg4(n + 3), w4 = ldg4(n + 4), w5 = ldg4(n + 5);
-	const uint32_t eb = __float_as_uint(w0.w);
-	const float adjx = __uint_as_float((eb & 0xffu) << 23) * rw.idx;
-	const float adjy = __uint_as_float(((eb >> 8) & 0xffu) << 23) * rw.idy;
-	const float adjz = __uint_as_float(((eb >> 16) & 0xffu) << 23) * rw.idz;
-	const float orgx = (w0.x - r.ox) * rw.idx, orgy = (w0.y - r.oy) * rw.idy, orgz = (w0.z - r.oz) * rw.idz;
-	/* The walk must never skip a child whose primitive the exact test would accept
-	 * (rays through shared edges and vertices, occluders within an ulp of the light
-	 * distance).  The plane distances q * adj + org carry a rounding error of at most
-	 * 6 ulp of (255 |adj| + |org|) against the true crossing (reciprocal, the two
-	 * products, the sums), so the near planes are pulled in and the far planes
-	 * pushed out by 16 ulp of (256 |adj| + |org|), per node and axis. */
-	const float ex = fmaf(fabsf(adjx), 256.f * kSlabUlps, fabsf(orgx) * kSlabUlps);
-	const float ey = fmaf(fabsf(adjy), 256.f * kSlabUlps, fabsf(orgy) * kSlabUlps);
-	const float ez = fmaf(fabsf(adjz), 256.f * kSlabUlps, fabsf(orgz) * kSlabUlps);
-	/* byte -> float costs one PRMT (2^23 + q in the mantissa); the 2^23 is taken
-	 * off in the constant term instead of per plane.  That term then has the
-	 * granularity of one quantisation step (ulp of 2^23 |adj|), so it is rounded
-	 * towards the outside of the slab. */
-	const float onx = __fmaf_rd(-8388608.f, adjx, orgx - ex), ofx = __fmaf_ru(-8388608.f, adjx, orgx + ex);
-	const float ony = __fmaf_rd(-8388608.f, adjy, orgy - ey), ofy = __fmaf_ru(-8388608.f, adjy, orgy + ey);
-	const float onz = __fmaf_rd(-8388608.f, adjz, orgz - ez), ofz = __fmaf_ru(-8388608.f, adjz, orgz + ez);
-	/* near / far planes by the sign of the direction */
-	const bool nx = rw.idx < 0.f, ny = rw.idy < 0.f, nz = rw.idz < 0.f;
-	const uint32_t nearx[2] = { __float_as_uint(nx ? w1.z : w1.x), __float_as_uint(nx ? w1.w : w1.y) };
-	const uint32_t farx[2] = { __float_as_uint(nx ? w1.x : w1.z), __float_as_uint(nx ? w1.y : w1.w) };
-	const uint32_t neary[2] = { __float_as_uint(ny ? w2.z : w2.x), __float_as_uint(ny ? w2.w : w2.y) };
-	const uint32_t fary[2] = { __float_as_uint(ny ? w2.x : w2.z), __float_as_uint(ny ? w2.y : w2.w) };
-	const uint32_t nearz[2] = { __float_as_uint(nz ? w3.z : w3.x), __float_as_uint(nz ? w3.w : w3.y) };
-	const uint32_t farz[2] = { __float_as_uint(nz ? w3.x : w3.z), __float_as_uint(nz ? w3.y : w3.w) };
-	const int code[8] = { __float_as_int(w4.x), __float_as_int(w4.y), __float_as_int(w4.z), __float_as_int(w4.w),
-		__float_as_int(w5.x), __float_as_int(w5.y), __float_as_int(w5.z), __float_as_int(w5.w) };
-#pragma unroll
-	for (int i = 0; i < 8; i++) {
-		const uint32_t sel = 0x7540u + (uint32_t)(i & 3); /* bytes: (b_i, 0x00, 0x00, 0x4b) */
-		const float tnx = fmaf(byte_to_float(nearx[i >> 2], sel), adjx, onx);
-		const float tny = fmaf(byte_to_float(neary[i >> 2], sel), adjy, ony);
-		const float tnz = fmaf(byte_to_float(nearz[i >> 2], sel), adjz, onz);
-		const float tfx = fmaf(byte_to_float(farx[i >> 2], sel), adjx, ofx);
-		const float tfy = fmaf(byte_to_float(fary[i >> 2], sel), adjy, ofy);
-		const float tfz = fmaf(byte_to_float(farz[i >> 2], sel), adjz, ofz);
-		const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
-		const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, dist));
-		if (code[i] != kStackSentinel)
-			Cnt<COUNT>::add(cn.box);
-		/* an empty child has near 255 / far 0 planes on every axis (and the sentinel code) */
-		const bool hit = tmin <= tmax && code[i] != kStackSentinel;
-		const bool to_stack = hit && code[i] >= 0, to_queue = hit && code[i] < 0;
-		if (to_stack)
-			stack[w.sp] = w.top;
-		if (to_queue)
-			q.put((w.qhead + w.qcount) & (kLeafQueue - 1), code[i]);
-		w.sp += to_stack ? 1 : 0;
-		w.top = to_stack ? code[i] : w.top;
-		w.qcount += to_queue ? 1 : 0;
+	const int node = group_base(w.inner) + group_take(w.inner);
+	const WideHits h = wide_node_test<COUNT>(sc, r, rw, dist, node, cn);
+	if (h.inner & 0xffu) {
+		if (w.inner & 0xffu)
+			st.put_inner(w.isp++, w.inner);
+		w.inner = h.inner;
+	} else if (!(w.inner & 0xffu) && w.isp > 0) {
+		w.inner = st.get_inner(--w.isp);
 	}
-	w.node = w.top;
-	w.top = w.sp > 0 ? stack[--w.sp] : kStackSentinel;
+	if (h.leaf & 0xffu) {
+		if (w.leaf & 0xffu)
+			st.put_leaf(w.lsp++, w.leaf);
+		w.leaf = h.leaf;
+	}
 }
 
-template <bool COUNT, class QUEUE>
+template <bool COUNT, class STACKS>
 __device__ __forceinline__ void shadow_prim_step(const DScene &sc, const Ray &r, float dist, int emitter_object, ShadowWalk &w,
-	const QUEUE &q, bool &blocked, float &lr, float &lg, float &lb, Counters &cn)
+	const STACKS &st, bool &blocked, float &lr, float &lg, float &lb, Counters &cn)
 {
-	if (w.leaf_left == 0) {
-		const int leaf = ~q.get(w.qhead);
-		w.qhead = (w.qhead + 1) & (kLeafQueue - 1);
-		w.qcount--;
-		w.leaf_first = leaf >> kLeafBits;
-		w.leaf_left = (leaf & ((1 << kLeafBits) - 1)) + 1;
-	}
+	const int slot = group_base(w.leaf) + group_take(w.leaf);
+	if (!(w.leaf & 0xffu) && w.lsp > 0)
+		w.leaf = st.get_leaf(--w.lsp);
 	float t;
 	uint32_t info;
 	int object;
-	const bool hit = hit_prim<COUNT>(sc, w.leaf_first, r, t, info, object, cn);
-	w.leaf_first++;
-	w.leaf_left--;
+	const bool hit = hit_prim<COUNT>(sc, slot, r, t, info, object, cn);
 	if (hit && t < dist && object != emitter_object) {
 		if (!(info & PRIM_TRANSPARENT)) {
 			blocked = true;
@@ -558,19 +598,18 @@ __device__ __forceinline__ bool trace_shadow_wide(const DScene &sc, const Ray &r
 		return true;
 	if (sc.num_nodes == 0)
 		return false;
-	int stack[kStackSize];
-	int slots[kLeafQueue];
-	const PrivateLeafQueue q = { slots };
+	uint32_t inner[kDeepStack], leaf[kLeafStack];
+	const PrivateStacks st = { inner, leaf };
 	ShadowWalk w;
 	shadow_walk_reset(w);
-	w.node = 0;
-	const RayWide rw = { safe_rcp(r.dx), safe_rcp(r.dy), safe_rcp(r.dz) };
+	w.inner = 1u; /* the root */
+	const WideRay rw = make_wide_ray(r);
 	bool blocked = false;
 	while (shadow_walk_busy(w)) {
 		if (shadow_can_inner(w))
-			shadow_inner_step<COUNT>(sc, r, rw, dist, w, stack, q, cn);
+			shadow_inner_step<COUNT>(sc, r, rw, dist, w, st, cn);
 		else
-			shadow_prim_step<COUNT>(sc, r, dist, emitter_object, w, q, blocked, lr, lg, lb, cn);
+			shadow_prim_step<COUNT>(sc, r, dist, emitter_object, w, st, blocked, lr, lg, lb, cn);
 	}
 	return blocked;
 }
@@ -611,8 +650,8 @@ __device__ __forceinline__ void hit_normal(const DScene &sc, const Hit &h, const
 		eps = px.x;
 		return;
 	}
-	const float4 p0 = ldg4(sc.prims + 3 * h.slot);
-	const float4 p1 = ldg4(sc.prims + 3 * h.slot + 1);
+	const float4 p0 = ldg4(sc.prims + 4 * (size_t)h.slot);
+	const float4 p1 = ldg4(sc.prims + 4 * (size_t)h.slot + 1);
 	const uint32_t info = __float_as_uint(p1.w);
 	material = info & PRIM_MATERIAL_MASK;
 	eps = p0.w;
@@ -622,7 +661,7 @@ __device__ __forceinline__ void hit_normal(const DScene &sc, const Hit &h, const
 		ny = __fmul_rn(__fsub_rn(__fadd_rn(__fmul_rn(r.dy, h.t), r.oy), p0.y), inv);
 		nz = __fmul_rn(__fsub_rn(__fadd_rn(__fmul_rn(r.dz, h.t), r.oz), p0.z), inv);
 	} else {
-		const float4 n = ldg4(sc.normals + h.slot);
+		const float4 n = ldg4(sc.prims + 4 * (size_t)h.slot + 3);
 		nx = n.x;
 		ny = n.y;
 		nz = n.z;

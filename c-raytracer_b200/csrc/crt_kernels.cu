@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	WarpShared *shared = reinterpret_cast<WarpShared *>(smem_raw);
-	int *wqueue = reinterpret_cast<int *>(smem_raw + sizeof(WarpShared) * kWarpsPerBlock);
+	uint32_t *wstacks = reinterpret_cast<uint32_t *>(smem_raw + sizeof(WarpShared) * kWarpsPerBlock);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp_local = threadIdx.x >> 5;
 	const uint32_t warp_global = blockIdx.x * kWarpsPerBlock + warp_local;
@@ -162,7 +162,9 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 	const DScene &sc = p.sc;
 	const crt_render_opts &o = p.o;
 	Counters cn = {};
-	int stack[kStackSize]; /* the lane's traversal stack (closest-hit walk, then the shadow walks) */
+	/* the lane's traversal stacks (closest-hit walk, then the shadow walks): shared memory, [slot][lane] */
+	const SharedStacks stacks(wstacks + warp_local * (kLaneStackWords * 32) + lane,
+		p.deep ? p.deep + (size_t)warp_global * p.deep_depth * 32 + lane : nullptr);
 
 	for (;;) {
 		/* ---- next tile of this shard ------------------------------------- */
@@ -264,7 +266,7 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 					if (r.inside >= 0)
 						found = hit_object<COUNT>(sc, r.inside, ray, hit, cn);
 					if (!found)
-						hit = trace_closest<COUNT>(sc, ray, stack, cn);
+						hit = trace_closest<COUNT>(sc, ray, stacks, cn);
 				}
 			}
 			const bool is_hit = have && hit.object >= 0;
@@ -358,13 +360,12 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 					bool have = false;
 					uint32_t w = 0, e_lane = 0;
 					Ray sr = { 0.f, 0.f, 0.f, 0.f, 0.f, 1.f };
-					RayWide rw = { 1.f, 1.f, 1.f };
+					WideRay rw = make_wide_ray(sr);
 					float dist = 0.f, d2 = 0.f, ir = 0.f, ig = 0.f, ib = 0.f;
 					int em_object = -1;
 					bool blocked = false;
 					ShadowWalk sw;
 					shadow_walk_reset(sw);
-					const SharedLeafQueue q(wqueue + warp_local * (kLeafQueue * 32) + lane);
 					for (;;) {
 						/* -- service: finished lanes shade and store, idle lanes fetch -- */
 						const bool walking = have && shadow_walk_busy(sw);
@@ -442,10 +443,8 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 									Cnt<COUNT>::add(cn.shadow);
 									blocked = shadow_planes<COUNT>(sc, sr, dist, ir, ig, ib, cn);
 									if (!blocked && sc.num_nodes != 0u) {
-										rw.idx = safe_rcp(sr.dx);
-										rw.idy = safe_rcp(sr.dy);
-										rw.idz = safe_rcp(sr.dz);
-										sw.node = 0; /* root of the wide tree; stack and queue are empty */
+										rw = make_wide_ray(sr);
+										sw.inner = 1u; /* the root of the wide tree; both stacks are empty */
 									}
 								}
 							}
@@ -466,12 +465,12 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 #pragma unroll 1
 								for (int k = 0; k < kInnerPerVote; k++)
 									if (have && shadow_can_inner(sw))
-										shadow_inner_step<COUNT>(sc, sr, rw, dist, sw, stack, q, cn);
+										shadow_inner_step<COUNT>(sc, sr, rw, dist, sw, stacks, cn);
 							} else {
 #pragma unroll 1
 								for (int k = 0; k < kPrimPerVote; k++)
 									if (have && shadow_can_prim(sw))
-										shadow_prim_step<COUNT>(sc, sr, dist, em_object, sw, q, blocked, ir, ig, ib, cn);
+										shadow_prim_step<COUNT>(sc, sr, dist, em_object, sw, stacks, blocked, ir, ig, ib, cn);
 							}
 						}
 						/* lanes whose walk ended are retired at the top of the loop */
@@ -635,8 +634,9 @@ __global__ void trace_closest_kernel(DScene sc, const float *rays, size_t n, int
 		return;
 	Counters cn = {};
 	const Ray r = { rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5], rays[6 * i], rays[6 * i + 1], rays[6 * i + 2] };
-	int stack[kStackSize];
-	const Hit h = trace_closest<false>(sc, r, stack, cn);
+	uint32_t inner[kDeepStack];
+	const PrivateStacks st = { inner, nullptr };
+	const Hit h = trace_closest<false>(sc, r, st, cn);
 	object[i] = h.object;
 	t[i] = h.t;
 	if (normal) {
@@ -704,7 +704,7 @@ void launch_raygen_rows(const crt_render_opts &o, float *row_pos, cudaStream_t s
 	raygen_rows_kernel<<<(o.height + threads - 1) / threads, threads, 0, stream>>>(o, row_pos);
 }
 
-constexpr size_t kRenderSmem = (sizeof(WarpShared) + sizeof(int) * kLeafQueue * 32) * kWarpsPerBlock;
+constexpr size_t kRenderSmem = (sizeof(WarpShared) + sizeof(uint32_t) * kLaneStackWords * 32) * kWarpsPerBlock;
 
 int render_blocks_per_sm(bool count)
 {

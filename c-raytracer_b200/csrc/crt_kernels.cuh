@@ -39,6 +39,7 @@ constexpr int kNumCounters = 11;
 #endif
 constexpr int kPendingWords = 13;          /* words per pending-ray record */
 constexpr int kSlots = 1024;               /* shadow-ray contribution slots per warp (one chunk) */
+constexpr int kLaneStackWords = kInnerStack + kLeafStack; /* shared-memory stack words per lane (crt_device.cuh SharedStacks) */
 constexpr int kRefill = 8;                 /* lanes fetch new shadow rays when fewer than this many are walking */
 
 struct RenderParams {
@@ -60,6 +61,8 @@ struct RenderParams {
 	float *pending;                 /* per-lane pending-ray stacks */
 	float *slots;                   /* per-warp shadow-ray contribution slots: 3 * kSlots floats each */
 	uint32_t pending_depth;
+	uint32_t *deep;                 /* spill strips of the inner stacks (trees deeper than kInnerStack), or null */
+	uint32_t deep_depth;            /* words per lane in a strip */
 };
 
 /* grid = number of persistent blocks */

@@ -1,39 +1,61 @@
 """Frame-parity metrics shared by tests/ and __graft_entry__.smoke() (pure numpy;
 the thing compared against -- reference golden frames or the CPU oracle -- is
-supplied by the caller).
+supplied by the caller).  Both sides draw the same structural RNG stream
+(include/crt_rng.h), so every frame can be compared pixel by pixel.
 
-Tolerances are those of BASELINE.json's deterministic tier (both sides draw the
-same structural RNG stream, include/crt_rng.h): rel-RMSE <= 1e-3 and <= 1 code
-after the reference's truncating 8-bit quantiser.  A pixel off by more than 1 %
-(+ 1e-4 of the frame maximum) is an OUTLIER.  Outliers are real and expected: a
-refracted or GI path (acosf / asinf / sinf, reference render.c:281-283, :324-338)
-that ends next to a silhouette or triangle edge goes to the neighbouring
-primitive under a last-ulp difference between CUDA's and glibc's libm.  The
-reference shows the same effect against itself (-Ofast vs -O2: up to 0.75 % of
-the pixels of scenetest2 differ by more than 1e-4), so up
-to max(2, 1e-3 * pixels) outliers are allowed (observed: 2 of 5184 on the
-871k-triangle dragon, 1 of 5184 on scene1 path traced, 0 on the other frames)
-and the rel-RMSE bound is applied to the remaining pixels."""
+Two tiers (BASELINE.json north_star):
+
+DETERMINISTIC tier -- no global illumination (-g ambient): whole-frame rel-RMSE
+<= 1e-3 over ALL pixels, at most 1e-4 of the pixels (SURVEY's allowance; 0 on
+every frame seen so far) off by more than 1 % (+ 1e-4 of the frame maximum),
+and <= 1 code after the reference's truncating 8-bit quantiser.
+
+STOCHASTIC tier -- path-traced frames (-g path): a refracted or GI path (acosf /
+asinf / sinf, reference render.c:270-286, :320-340) that ends next to a
+silhouette or triangle edge goes to the neighbouring primitive under a last-ulp
+difference between CUDA's and glibc's libm, which changes that pixel by the
+weight of one path.  Such OUTLIER pixels are counted (at most max(2, 1e-3 *
+pixels); observed: 3 of 5184 on the 871k-triangle dragon, 1 of 1296 on scene1)
+and the 1e-3 rel-RMSE bound is applied to the remaining pixels -- AND the
+whole-frame rel-RMSE over all pixels, outliers included, must stay within
+SURVEY's Tier-2 bound: twice the reference's OWN seed-to-seed rel-RMSE at the
+same flags (measured by tests/golden/make_golden.py and stored in every golden
+file; 0.04 .. 0.4 at the sample counts used here -- the observed whole-frame
+error is about 2e-3, a hundred times below it)."""
 import numpy as np
 
 REL_RMSE_TOL = 1e-3
 OUTLIER_REL, OUTLIER_ABS = 1e-2, 1e-4
-OUTLIER_PIXELS = 1e-3
+OUTLIER_PIXELS_STOCHASTIC = 1e-3
+OUTLIER_PIXELS_DETERMINISTIC = 1e-4
+TIER2_FACTOR = 2.0
+OUTLIER_PIXELS = OUTLIER_PIXELS_STOCHASTIC  # paths that may flip (ray-count allowances in the tests)
 
 
 def rel_rmse(a, b):
     return float(np.linalg.norm(a.astype(np.float64) - b) / max(np.linalg.norm(b.astype(np.float64)), 1e-30))
 
 
-def frame_parity(raster, ref_raster):
-    """-> dict(outliers, allowed, rel_rmse, rel_rmse_all, ok)"""
+def frame_parity(raster, ref_raster, seed_to_seed=None):
+    """seed_to_seed: None or 0 -> deterministic tier; the reference's own seed-to-seed
+    rel-RMSE at the same flags -> stochastic tier.
+    -> dict(tier, outliers, allowed, rel_rmse, rel_rmse_all, bound_all, ok)"""
     pixels = raster.shape[0] * raster.shape[1]
     diff = np.abs(raster.astype(np.float64) - ref_raster).max(axis=2)
     bound = OUTLIER_REL * np.abs(ref_raster).max(axis=2) + OUTLIER_ABS * float(ref_raster.max())
     outlier = diff > bound
     keep = ~outlier
     r = rel_rmse(raster[keep], ref_raster[keep])
-    allowed = max(2, int(pixels * OUTLIER_PIXELS))
-    return {"outliers": int(outlier.sum()), "allowed": allowed, "rel_rmse": r,
-            "rel_rmse_all": rel_rmse(raster, ref_raster),
-            "ok": bool(np.isfinite(raster).all() and outlier.sum() <= allowed and r <= REL_RMSE_TOL)}
+    r_all = rel_rmse(raster, ref_raster)
+    finite = bool(np.isfinite(raster).all())
+    if seed_to_seed:
+        tier = "stochastic"
+        allowed = max(2, int(pixels * OUTLIER_PIXELS_STOCHASTIC))
+        bound_all = TIER2_FACTOR * float(seed_to_seed)
+    else:
+        tier = "deterministic"
+        allowed = int(pixels * OUTLIER_PIXELS_DETERMINISTIC)
+        bound_all = REL_RMSE_TOL
+    ok = finite and outlier.sum() <= allowed and r <= REL_RMSE_TOL and r_all <= bound_all
+    return {"tier": tier, "outliers": int(outlier.sum()), "allowed": allowed, "rel_rmse": r,
+            "rel_rmse_all": r_all, "bound_all": bound_all, "ok": bool(ok)}

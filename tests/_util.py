@@ -22,7 +22,8 @@ def load_golden_image(name):
     g = np.load(os.path.join(GOLDEN, f"image_{name}.npz"))
     flags = [str(f) for f in g["flags"]]
     return {"raster": g["raster"], "z": g["z"], "scene": str(g["scene"]), "width": int(g["width"]),
-            "height": int(g["height"]), "flags": flags, "cast_ray": int(g["cast_ray"]), "shadow": int(g["shadow"])}
+            "height": int(g["height"]), "flags": flags, "cast_ray": int(g["cast_ray"]), "shadow": int(g["shadow"]),
+            "seed_to_seed": float(g["seed_to_seed_rel_rmse"])}
 
 
 def open_case(case):

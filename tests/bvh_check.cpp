@@ -30,14 +30,6 @@ static bool contains(const float *lo, const float *hi, const Aabb &b)
 	return true;
 }
 
-static float plane(float origin, uint32_t exponent, uint8_t q)
-{
-	const uint32_t bits = exponent << 23;
-	float scale;
-	memcpy(&scale, &bits, 4);
-	return origin + (float)q * scale; /* the device evaluates fl(q * scale + origin) too */
-}
-
 int main(int argc, char **argv)
 {
 	if (argc < 4)
@@ -120,57 +112,84 @@ int main(int argc, char **argv)
 		CHECK(covered[s] == 1, "primitive slot %u is in %u leaves (the shadow query tints once per primitive)", s, covered[s]);
 	CHECK(depth_seen <= a.max_depth && a.max_depth <= 128, "depth %u (reported %u) exceeds the device stack", depth_seen, a.max_depth);
 
-	/* 8-wide collapse and quantisation: same coverage, quantised boxes contain the exact ones */
-	WideResult w;
-	build_wide(a, w, 0);
-	std::vector<QuantNode> q;
-	quantize_wide(w, q);
-	CHECK(q.size() == w.nodes.size() && !w.nodes.empty(), "no wide nodes");
+	/* 8-wide device tree: every primitive in exactly one leaf slot, slots of a kind contiguous (leaves,
+	 * then inner children), child nodes and primitives of a node contiguous, and the stored boxes
+	 * -- centre +- (half extent - slack) on the node's grid -- contain the exact ones */
+	WideTree w;
+	build_wide(boxes, a, w);
+	CHECK(!w.nodes.empty() && w.order.size() == n, "no wide nodes / order has %zu entries", w.order.size());
+	std::fill(seen.begin(), seen.end(), 0u);
+	for (uint32_t p : w.order) {
+		CHECK(p < n, "wide order entry %u out of range", p);
+		seen[p]++;
+	}
+	for (uint32_t i = 0; i < n; i++)
+		CHECK(seen[i] == 1, "box %u appears %u times in the wide order", i, seen[i]);
 	std::fill(covered.begin(), covered.end(), 0u);
-	std::vector<int32_t> wstack = { 0 };
+	struct WItem { int32_t node; uint32_t depth; Aabb bound; bool bounded; };
+	std::vector<WItem> wstack;
+	wstack.push_back({ 0, 1, Aabb(), false });
 	size_t visited = 0;
+	uint32_t wdepth = 0;
 	while (!wstack.empty()) {
-		const int32_t id = wstack.back();
+		const WItem it = wstack.back();
 		wstack.pop_back();
-		CHECK(id >= 0 && (size_t)id < w.nodes.size(), "wide node index %d out of range", id);
+		CHECK(it.node >= 0 && (size_t)it.node < w.nodes.size(), "wide node index %d out of range", it.node);
 		visited++;
-		const WideNode &wn = w.nodes[id];
-		const QuantNode &qn = q[id];
+		wdepth = std::max(wdepth, it.depth);
+		const WideNode &wn = w.nodes[it.node];
+		const uint32_t lmask = (wn.meta >> 8) & 0xffu, imask = (wn.meta >> 16) & 0xffu;
+		const int nl = __builtin_popcount(lmask), ni = __builtin_popcount(imask);
+		CHECK(lmask == (1u << nl) - 1u && imask == (((1u << ni) - 1u) << nl) && nl + ni >= 1 && nl + ni <= 8,
+			"slots of wide node %d are not leaves-then-inner (masks %02x %02x)", it.node, lmask, imask);
+		const int e = (int)(wn.meta & 0xffu) - 127;
+		CHECK(e >= -40 && e <= 60, "grid exponent %d of node %d out of range", e, it.node);
+		const double scale = std::ldexp(1.0, e);
 		for (int j = 0; j < 8; j++) {
-			int32_t code;
-			memcpy(&code, &wn.b[j][2], 4);
-			CHECK(code == qn.code[j], "codes of wide node %d differ", id);
-			if (code == kWideEmpty) {
-				for (int k = 0; k < 3; k++)
-					CHECK(qn.q[k][0][j] == 255 && qn.q[k][1][j] == 0, "empty child %d of node %d is not inverted", j, id);
-				continue;
-			}
-			Aabb exact;
-			exact.lo[0] = wn.a[j][0]; exact.lo[1] = wn.a[j][1]; exact.lo[2] = wn.a[j][2];
-			exact.hi[0] = wn.a[j][3]; exact.hi[1] = wn.b[j][0]; exact.hi[2] = wn.b[j][1];
-			float lo[3], hi[3];
+			const bool used = ((lmask | imask) >> j) & 1u;
+			Aabb q;
 			for (int k = 0; k < 3; k++) {
-				const uint32_t e = (qn.exponents >> (8 * k)) & 0xffu;
-				lo[k] = plane(qn.origin[k], e, qn.q[k][0][j]);
-				hi[k] = plane(qn.origin[k], e, qn.q[k][1][j]);
+				const float c = half_value(wn.plane[k][0][j]), h = half_value(wn.plane[k][1][j]);
+				if (!used) {
+					CHECK(std::isinf(h) && h < 0.f, "empty slot %d of node %d is not inverted", j, it.node);
+					continue;
+				}
+				CHECK(c >= 0.f && c <= kWideGrid && h >= kWideSlack && std::floor(2.f * c) == 2.f * c && std::floor(2.f * h) == 2.f * h,
+					"slot %d of node %d: centre %g / half extent %g off the half-unit grid", j, it.node, c, h);
+				CHECK(c - (h - kWideSlack) >= 0.f && c + (h - kWideSlack) <= kWideGrid, "slot %d of node %d leaves the grid cube", j, it.node);
+				q.lo[k] = (float)((double)wn.origin[k] + ((double)c - ((double)h - kWideSlack)) * scale);
+				q.hi[k] = (float)((double)wn.origin[k] + ((double)c + ((double)h - kWideSlack)) * scale);
+				/* the float conversion above may round inwards by an ulp: compare in double */
+				const double lo = (double)wn.origin[k] + ((double)c - ((double)h - kWideSlack)) * scale;
+				const double hi = (double)wn.origin[k] + ((double)c + ((double)h - kWideSlack)) * scale;
+				q.lo[k] = (float)lo > lo ? std::nextafter((float)lo, -INFINITY) : (float)lo;
+				q.hi[k] = (float)hi < hi ? std::nextafter((float)hi, INFINITY) : (float)hi;
 			}
-			CHECK(contains(lo, hi, exact), "quantised box of child %d of wide node %d is not conservative", j, id);
-			if (code >= 0) {
-				wstack.push_back(code);
+			if (!used)
+				continue;
+			if (it.bounded)
+				for (int k = 0; k < 3; k++)
+					CHECK(q.lo[k] >= it.bound.lo[k] - 8.0 * scale && q.hi[k] <= it.bound.hi[k] + 8.0 * scale,
+						"child box %d of node %d sticks out of the node's own box", j, it.node);
+			if ((imask >> j) & 1u) {
+				const int32_t child = wn.child_base + j;
+				CHECK(child > it.node && (size_t)child < w.nodes.size() && w.nodes[child].parent == it.node,
+					"inner slot %d of node %d -> %d: bad child index or parent link", j, it.node, child);
+				wstack.push_back({ child, it.depth + 1, q, true });
 				continue;
 			}
-			const uint32_t leaf = (uint32_t)~code;
-			const uint32_t first = leaf >> kLeafCountBits, count = (leaf & ((1u << kLeafCountBits) - 1u)) + 1u;
-			for (uint32_t s = first; s < first + count; s++) {
-				CHECK(s < n, "wide leaf slot %u out of range", s);
-				covered[s]++;
-				CHECK(contains(exact.lo, exact.hi, boxes[a.order[s]]), "wide leaf box does not contain slot %u", s);
-			}
+			const int32_t s = wn.prim_base + j;
+			CHECK(s >= 0 && (uint32_t)s < n, "leaf slot %d of node %d -> primitive slot %d out of range", j, it.node, s);
+			covered[s]++;
+			CHECK(contains(q.lo, q.hi, boxes[w.order[s]]), "stored box of leaf slot %d of node %d does not contain primitive slot %d", j, it.node, s);
 		}
+		/* an inner child's stored box must contain everything below it: checked through `bound` one level down,
+		 * and transitively for the primitives (each node's leaf boxes contain their primitives) */
 	}
 	CHECK(visited == w.nodes.size(), "%zu of %zu wide nodes reachable", visited, w.nodes.size());
 	for (uint32_t s = 0; s < n; s++)
-		CHECK(covered[s] == 1, "primitive slot %u is in %u wide leaves", s, covered[s]);
-	printf("ok n %u nodes %zu leaves %u depth %u wide %zu depth %u\n", n, a.nodes.size(), leaves, a.max_depth, w.nodes.size(), w.max_depth);
+		CHECK(covered[s] == 1, "primitive slot %u is in %u wide leaf slots", s, covered[s]);
+	CHECK(wdepth == w.max_depth && w.max_depth <= kWideMaxDepth, "wide depth %u (reported %u) exceeds the device stacks", wdepth, w.max_depth);
+	printf("ok n %u nodes %zu leaves %u depth %u wide %zu depth %u cost %.2f\n", n, a.nodes.size(), leaves, a.max_depth, w.nodes.size(), w.max_depth, w.cost);
 	return 0;
 }

@@ -126,12 +126,25 @@ def main():
         if only and only not in name:
             continue
         raster, z, cnt = oracle.ref_render(os.path.join("scenes", scene + ".json"), w, h, flags, seed=seed_of(flags))
-        np.savez_compressed(os.path.join(HERE, f"image_{name}.npz"), raster=raster, z=z,
+        # stochastic configurations (-g path) also carry the reference's own seed-to-seed rel-RMSE at the
+        # same flags: SURVEY 8(d) Tier 2 bounds the whole-frame error by twice that number
+        seed_rmse = 0.0
+        if "path" in flags:
+            bare = [f for i, f in enumerate(flags) if f != "--seed" and (i == 0 or flags[i - 1] != "--seed")]
+            other, _, _ = oracle.ref_render(os.path.join("scenes", scene + ".json"), w, h, bare, seed=seed_of(flags) + 1)
+            seed_rmse = float(np.linalg.norm(other.astype(np.float64) - raster) / np.linalg.norm(raster.astype(np.float64)))
+        out = os.path.join(HERE, f"image_{name}.npz")
+        same = ""
+        if os.path.exists(out):
+            old = np.load(out)
+            same = " (frame unchanged)" if np.array_equal(old["raster"], raster) and np.array_equal(old["z"], z) else " (FRAME CHANGED)"
+        np.savez_compressed(out, raster=raster, z=z,
                             cast_ray=cnt["cast_ray"], shadow=cnt["shadow"], scene=scene, width=w, height=h,
-                            flags=np.array(flags, dtype=str))
-        print(f"image_{name}: {w}x{h} cast_ray {cnt['cast_ray']} shadow {cnt['shadow']} max {raster.max():.4f}")
+                            flags=np.array(flags, dtype=str), seed_to_seed_rel_rmse=seed_rmse)
+        print(f"image_{name}: {w}x{h} cast_ray {cnt['cast_ray']} shadow {cnt['shadow']} max {raster.max():.4f} "
+              f"seed-to-seed {seed_rmse:.3e}{same}")
 
-    if only:
+    if only or os.environ.get("GOLDEN_IMAGES_ONLY"):
         return
     for scene in RAY_SCENES:
         sc = host.Scene(os.path.join(ROOT, "scenes", scene + ".json"))

@@ -1,9 +1,9 @@
 """Host tree builders (c-raytracer_b200/csrc/bvh_build.cpp): the binned-SAH
-binary tree, its 8-wide collapse and the quantisation, checked by a small C++
+binary tree (one primitive per leaf) and its 8-wide collapse into the 128-byte device nodes, checked by a small C++
 program (tests/bvh_check.cpp) on seeded boxes -- every primitive in exactly one
-leaf (the shadow query tints once per transparent primitive, reference
-accel.c:369-373), boxes contain what is below them, the quantised boxes are
-conservative, the depth fits the device stack, and the multi-threaded build
+leaf slot (the shadow query tints once per transparent primitive, reference
+accel.c:369-373), the stored half-precision boxes contain what is below them, children and primitives of a node are
+contiguous, the depth fits the device stacks, and the multi-threaded build
 gives the single-threaded tree bit for bit."""
 import os
 import subprocess

@@ -288,3 +288,43 @@ def test_engine_cli_help_and_usage():
     assert out.returncode == 1 and out.stdout.startswith("Too few arguments.")
     out = subprocess.run([exe, "missing.json", "o.tif", "8", "8"], capture_output=True, text=True, cwd=ROOT)
     assert out.returncode == 1 and "Unable to open scene file [missing.json]." in out.stdout
+
+
+def test_parity_tiers():
+    """c-raytracer_b200/parity.py: the deterministic tier bounds the whole frame, the stochastic
+    tier bounds the whole frame by twice the reference's seed-to-seed rel-RMSE on top of the
+    outlier-excluded check."""
+    from c_raytracer_b200 import parity
+    rng = np.random.default_rng(0)
+    ref = rng.random((100, 200, 3)).astype(np.float32)
+    ok = parity.frame_parity(ref * np.float32(1 + 1e-5), ref)
+    assert ok["ok"] and ok["tier"] == "deterministic" and ok["allowed"] == 2 and ok["outliers"] == 0
+    one_bad = ref.copy()
+    one_bad[3, 4] += 0.02  # 1 of 20000 pixels: within the 1e-4 allowance, and the whole frame stays below 1e-3
+    assert parity.frame_parity(one_bad, ref)["ok"]
+    one_bad[3, 4] += 0.5    # ... but not when that one pixel lifts the whole-frame error above 1e-3
+    assert not parity.frame_parity(one_bad, ref)["ok"]
+    many_bad = ref.copy()
+    many_bad[:3, :3] += 0.5  # 9 outliers > 2 allowed
+    assert not parity.frame_parity(many_bad, ref)["ok"]
+    # stochastic tier: the same 9 flipped pixels pass (<= 1e-3 of 20000 = 20) while the whole frame stays within 2 x seed-to-seed
+    st = parity.frame_parity(many_bad, ref, seed_to_seed=0.1)
+    assert st["ok"] and st["tier"] == "stochastic" and st["bound_all"] == 0.2 and st["rel_rmse_all"] > st["rel_rmse"]
+    # ... and fail when the whole-frame error exceeds that bound although the outlier count is fine
+    assert not parity.frame_parity(many_bad, ref, seed_to_seed=1e-3)["ok"]
+    small = ref[:10, :10]
+    assert parity.frame_parity(small, small)["allowed"] == 0  # deterministic tier, 100 pixels: no outlier allowed
+
+
+def test_bench_goldens_are_complete():
+    """tests/golden/bench_*.npz (the benchmark flags on the benchmark geometry, rendered by the
+    unmodified reference) carry the frame, the ray counts, the mesh hash and the Tier-2 number."""
+    import glob
+    files = sorted(glob.glob(os.path.join(GOLDEN, "bench_*.npz")))
+    assert len(files) >= 2
+    for f in files:
+        g = np.load(f)
+        h, w = int(g["height"]), int(g["width"])
+        assert g["raster"].shape == (h, w, 3) and g["z"].shape == (h, w)
+        assert 0.01 < float(g["seed_to_seed_rel_rmse"]) < 1.0
+        assert len(str(g["mesh_sha256"])) == 64 and int(g["shadow"]) > 0

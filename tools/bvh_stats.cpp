@@ -1,8 +1,9 @@
 /* bvh_stats -- offline statistics of the two trees built from a binary STL
  * (fill of the 8-wide nodes, surface-area estimate of visits per random ray).
  *   g++ -O2 -std=c++17 -Ic-raytracer_b200/csrc tools/bvh_stats.cpp c-raytracer_b200/csrc/bvh_build.cpp -o build/bvh_stats
- *   build/bvh_stats meshes/dragon.stl [merge_prims] */
+ *   build/bvh_stats meshes/dragon.stl */
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -45,62 +46,56 @@ int main(int argc, char **argv)
 	fclose(f);
 	BvhResult bvh;
 	build_bvh(boxes, bvh);
-	WideResult wide;
-	build_wide(bvh, wide, argc > 2 ? atoi(argv[2]) : 0);
-	size_t hist[9] = { 0 }, leaf_children = 0, inner_children = 0, leaf_prims = 0;
-	double visits = 0, slots = 0, filled = 0, prim_tests = 0;
-	float root_area = 0;
-	std::vector<float> area(wide.nodes.size(), 0.f);
-	/* node area = area of the union of its children; the root first */
-	for (size_t i = 0; i < wide.nodes.size(); i++) {
-		const WideNode &w = wide.nodes[i];
+	WideTree wide;
+	build_wide(boxes, bvh, wide);
+	/* per node: its own box is the parent's stored box of it; the surface-area estimate uses the stored
+	 * (quantised, padded) boxes, i.e. what the device walk actually tests */
+	size_t hist[9] = { 0 }, leaf_children = 0, inner_children = 0;
+	double visits = 0, filled = 0, prim_tests = 0;
+	std::vector<double> area(wide.nodes.size(), 0.0);
+	auto stored_area = [&](const WideNode &w, int j) {
+		double ext[3];
+		const double scale = std::ldexp(1.0, (int)(w.meta & 0xffu) - 127);
+		for (int k = 0; k < 3; k++)
+			ext[k] = 2.0 * half_value(w.plane[k][1][j]) * scale;
+		return ext[0] * ext[1] + ext[1] * ext[2] + ext[2] * ext[0];
+	};
+	{
 		float lo[3] = { 1e30f, 1e30f, 1e30f }, hi[3] = { -1e30f, -1e30f, -1e30f };
-		int kids = 0;
-		for (int j = 0; j < 8; j++) {
-			int32_t code;
-			memcpy(&code, &w.b[j][2], 4);
-			if (code == kWideEmpty)
-				continue;
-			kids++;
-			const float clo[3] = { w.a[j][0], w.a[j][1], w.a[j][2] }, chi[3] = { w.a[j][3], w.b[j][0], w.b[j][1] };
+		for (const Aabb &b : boxes)
 			for (int k = 0; k < 3; k++) {
-				lo[k] = std::min(lo[k], clo[k]);
-				hi[k] = std::max(hi[k], chi[k]);
+				lo[k] = std::min(lo[k], b.lo[k]);
+				hi[k] = std::max(hi[k], b.hi[k]);
 			}
-		}
-		hist[kids]++;
-		area[i] = half_area(lo, hi);
-		if (i == 0)
-			root_area = area[0];
+		area[0] = half_area(lo, hi);
 	}
 	for (size_t i = 0; i < wide.nodes.size(); i++) {
 		const WideNode &w = wide.nodes[i];
-		const double p = area[i] / root_area; /* chance that a random line through the root box meets this node */
+		const uint32_t lmask = (w.meta >> 8) & 0xffu, imask = (w.meta >> 16) & 0xffu;
+		hist[__builtin_popcount(lmask | imask)]++;
+		const double p = area[i] / area[0]; /* chance that a random line through the root box meets this node */
 		visits += p;
-		slots += 8 * p;
 		for (int j = 0; j < 8; j++) {
-			int32_t code;
-			memcpy(&code, &w.b[j][2], 4);
-			if (code == kWideEmpty)
+			if (!(((lmask | imask) >> j) & 1u))
 				continue;
 			filled += p;
-			if (code < 0) {
-				const uint32_t cnt = ((~code) & 7) + 1;
+			const double a = stored_area(w, j);
+			if ((lmask >> j) & 1u) {
 				leaf_children++;
-				leaf_prims += cnt;
-				const float clo[3] = { w.a[j][0], w.a[j][1], w.a[j][2] }, chi[3] = { w.a[j][3], w.b[j][0], w.b[j][1] };
-				prim_tests += cnt * half_area(clo, chi) / root_area;
+				prim_tests += a / area[0];
 			} else {
 				inner_children++;
+				area[w.child_base + j] = a; /* children come after their parent */
 			}
 		}
 	}
-	printf("prims %u  bvh2 nodes %zu depth %u | wide nodes %zu depth %u\n", n, bvh.nodes.size(), bvh.max_depth, wide.nodes.size(), wide.max_depth);
+	printf("prims %u  bvh2 nodes %zu depth %u | wide nodes %zu depth %u, modelled cost %.2f\n", n, bvh.nodes.size(), bvh.max_depth,
+		wide.nodes.size(), wide.max_depth, wide.cost);
 	printf("children per wide node:");
 	for (int k = 0; k <= 8; k++)
 		printf(" %d:%zu", k, hist[k]);
-	printf("\nmean fill %.2f  leaf children %zu (%.2f prims each)  inner children %zu\n",
-		(double)(leaf_children + inner_children) / wide.nodes.size(), leaf_children, (double)leaf_prims / leaf_children, inner_children);
-	printf("surface-area estimate per random line: node visits %.1f, filled slots %.1f (of %.1f), prim tests %.1f\n", visits, filled, slots, prim_tests);
+	printf("\nmean fill %.2f  leaf slots %zu  inner slots %zu\n",
+		(double)(leaf_children + inner_children) / wide.nodes.size(), leaf_children, inner_children);
+	printf("surface-area estimate per random line (stored boxes): node visits %.1f, filled slots %.1f, primitive tests %.1f\n", visits, filled, prim_tests);
 	return 0;
 }
