@@ -68,7 +68,8 @@ class Stats(C.Structure):
         ("rays_closest", C.c_uint64), ("rays_shadow", C.c_uint64), ("box_tests", C.c_uint64),
         ("tri_tests", C.c_uint64 * 4), ("sphere_tests", C.c_uint64 * 2), ("plane_tests", C.c_uint64),
         ("nodes_shaded", C.c_uint64), ("kernel_ms", C.c_double), ("total_ms", C.c_double),
-        ("reserved", C.c_uint64 * 4),
+        ("node_steps", C.c_uint64), ("node_step_lanes", C.c_uint64), ("node_step_idle", C.c_uint64),
+        ("prim_steps", C.c_uint64), ("prim_step_lanes", C.c_uint64), ("prim_step_idle", C.c_uint64),
     ]
 
     def as_dict(self):
@@ -78,6 +79,8 @@ class Stats(C.Structure):
             "sphere_tests": [int(x) for x in self.sphere_tests], "plane_tests": int(self.plane_tests),
             "nodes_shaded": int(self.nodes_shaded), "kernel_ms": float(self.kernel_ms),
             "total_ms": float(self.total_ms),
+            "node_steps": int(self.node_steps), "node_step_lanes": int(self.node_step_lanes), "node_step_idle": int(self.node_step_idle),
+            "prim_steps": int(self.prim_steps), "prim_step_lanes": int(self.prim_step_lanes), "prim_step_idle": int(self.prim_step_idle),
         }
 
 

@@ -549,6 +549,12 @@ int crt_render_device_sync(crt_scene *s, crt_stats *stats)
 			stats->sphere_tests[1] = c[8];
 			stats->plane_tests = c[9];
 			stats->nodes_shaded = c[10];
+			stats->node_steps = c[11];
+			stats->node_step_lanes = c[12];
+			stats->node_step_idle = c[13];
+			stats->prim_steps = c[14];
+			stats->prim_step_lanes = c[15];
+			stats->prim_step_idle = c[16];
 		}
 	}
 	return CRT_OK;

@@ -65,6 +65,9 @@ struct DScene {
 /* per-lane test counters of the instrumented kernel instance */
 struct Counters {
 	uint32_t closest, shadow, box, tri0, tri1, tri2, tri3, sph0, sph1, plane, shaded;
+	/* walk efficiency of the direct-light loop, counted by lane 0 per warp-level step: steps of each kind, lanes
+	 * that took them, and why the others did not (no ray: waiting for a refill; other: only work of the other kind) */
+	uint32_t node_steps, node_lanes, node_noray, prim_steps, prim_lanes, prim_noray;
 };
 
 template <bool COUNT>
@@ -89,6 +92,7 @@ __device__ __forceinline__ float dot3(float ax, float ay, float az, float bx, fl
 }
 
 __device__ __forceinline__ float4 ldg4(const float4 *p) { return __ldg(p); }
+
 
 /* ---- primitive tests ------------------------------------------------------
  * Same formulation, comparisons and epsilon rules as the reference, so that
@@ -234,7 +238,10 @@ __device__ __forceinline__ bool hit_prim(const DScene &sc, int slot, const Ray &
  * of (base << 8 | mask) words per kind and a short stack of such words. */
 
 constexpr int kInnerStack = 12;  /* inner-group entries per lane kept in shared memory; deeper ones spill (DeepStack) */
-constexpr int kLeafStack = 8;    /* leaf-group entries per lane ([slot][lane]); a node visit adds at most one */
+#ifndef CRT_LEAF_STACK
+#define CRT_LEAF_STACK 8
+#endif
+constexpr int kLeafStack = CRT_LEAF_STACK;    /* leaf-group entries per lane ([slot][lane]); a node visit adds at most one */
 constexpr int kDeepStack = 64;   /* >= kWideMaxDepth */
 
 /* ray constants of the wide walk (beside the ray itself) */

@@ -98,6 +98,19 @@ __device__ __forceinline__ uint32_t nth_set_bit(uint32_t mask, uint32_t n)
 	return pos;
 }
 
+/* which emitter and which of its samples light index li is; false: that emitter is the hit object itself (no ray) */
+__device__ __forceinline__ bool light_of_index(const DScene &sc, uint32_t li, int skip_e, uint32_t &ei, uint32_t &l)
+{
+	ei = 0;
+	while (ei + 1u < sc.num_emitters && li >= sc.emitters[ei + 1u].first_light)
+		ei++;
+	/* draw index counts only the emitters that are sampled, in order */
+	l = li;
+	if (skip_e >= 0 && (int)ei > skip_e)
+		l -= sc.emitters[skip_e].num_lights;
+	return (int)ei != skip_e;
+}
+
 /* eye-segment attenuation applied to every cast_ray result (render.c:292-301) */
 __device__ __forceinline__ float eye_attenuation(const crt_render_opts &o, float t)
 {
@@ -417,18 +430,12 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 								const uint32_t li = s0 + (w - q * cL);
 								e_lane = nth_set_bit(lit_mask, p0 + q);
 								/* which emitter, which sample */
-								uint32_t ei = 0;
-								while (ei + 1u < sc.num_emitters && li >= sc.emitters[ei + 1u].first_light)
-									ei++;
+								uint32_t ei, l;
+								const bool sampled = light_of_index(sc, li, __float_as_int(ws.entry[E_SKIP][e_lane]), ei, l);
 								const DEmitter &em = sc.emitters[ei];
-								const int skip_e = __float_as_int(ws.entry[E_SKIP][e_lane]);
-								if ((int)ei == skip_e) {
+								if (!sampled) {
 									blocked = true; /* the hit object is not its own light (render.c:172): no ray */
 								} else {
-									/* draw index counts only the emitters that are sampled, in order */
-									uint32_t l = li;
-									if (skip_e >= 0 && (int)ei > skip_e)
-										l -= sc.emitters[skip_e].num_lights;
 									const float Px = ws.entry[E_PX][e_lane], Py = ws.entry[E_PY][e_lane], Pz = ws.entry[E_PZ][e_lane];
 									float lx, ly, lz;
 									light_point(em, Px, Py, Pz, __float_as_uint(ws.entry[E_NODE][e_lane]), 2u * l, lx, ly, lz);
@@ -463,14 +470,34 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 							if (__popc(bi) * kInnerWeight >= __popc(bp) * kPrimWeight) {
 								/* several steps per vote; rolled loops keep the walk inside the instruction cache */
 #pragma unroll 1
-								for (int k = 0; k < kInnerPerVote; k++)
-									if (have && shadow_can_inner(sw))
+								for (int k = 0; k < kInnerPerVote; k++) {
+									const bool go = have && shadow_can_inner(sw);
+									if (COUNT) {
+										const unsigned g = __ballot_sync(kFull, go), h = __ballot_sync(kFull, have);
+										if (lane == 0 && g) {
+											cn.node_steps++;
+											cn.node_lanes += (uint32_t)__popc(g);
+											cn.node_noray += 32u - (uint32_t)__popc(h);
+										}
+									}
+									if (go)
 										shadow_inner_step<COUNT>(sc, sr, rw, dist, sw, stacks, cn);
+								}
 							} else {
 #pragma unroll 1
-								for (int k = 0; k < kPrimPerVote; k++)
-									if (have && shadow_can_prim(sw))
+								for (int k = 0; k < kPrimPerVote; k++) {
+									const bool go = have && shadow_can_prim(sw);
+									if (COUNT) {
+										const unsigned g = __ballot_sync(kFull, go), h = __ballot_sync(kFull, have);
+										if (lane == 0 && g) {
+											cn.prim_steps++;
+											cn.prim_lanes += (uint32_t)__popc(g);
+											cn.prim_noray += 32u - (uint32_t)__popc(h);
+										}
+									}
+									if (go)
 										shadow_prim_step<COUNT>(sc, sr, dist, em_object, sw, stacks, blocked, ir, ig, ib, cn);
+								}
 							}
 						}
 						/* lanes whose walk ended are retired at the top of the loop */

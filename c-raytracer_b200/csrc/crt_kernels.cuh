@@ -11,7 +11,10 @@ namespace crt {
 
 constexpr int kTileW = CRT_TILE_W, kTileH = CRT_TILE_H;      /* one warp owns an 8x4 pixel tile: lane = pixel */
 constexpr int kChunkTiles = CRT_SHARD_CHUNK_TILES;            /* sharding granularity (crt_render_opts.shard_*) */
-constexpr int kWarpsPerBlock = 8;
+#ifndef CRT_WARPS_PER_BLOCK
+#define CRT_WARPS_PER_BLOCK 8
+#endif
+constexpr int kWarpsPerBlock = CRT_WARPS_PER_BLOCK;
 constexpr int kBlockThreads = kWarpsPerBlock * 32;
 #ifndef CRT_INNER_PER_VOTE
 #define CRT_INNER_PER_VOTE 3
@@ -27,7 +30,7 @@ constexpr int kBlockThreads = kWarpsPerBlock * 32;
 #endif
 constexpr int kInnerPerVote = CRT_INNER_PER_VOTE, kPrimPerVote = CRT_PRIM_PER_VOTE; /* unit steps per warp vote */
 constexpr int kInnerWeight = CRT_INNER_WEIGHT, kPrimWeight = CRT_PRIM_WEIGHT;       /* node step iff ready_inner * Wi >= ready_prim * Wp */
-constexpr int kNumCounters = 11;
+constexpr int kNumCounters = 17;
 #ifndef CRT_MICRO_PIXELS
 #define CRT_MICRO_PIXELS 2                 /* pixels per work unit in the final phase of a frame */
 #endif

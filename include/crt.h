@@ -190,7 +190,11 @@ typedef struct crt_stats {
 	uint64_t nodes_shaded; /* cast_ray invocations that found a hit */
 	double kernel_ms;      /* device time of the trace kernel(s), CUDA events */
 	double total_ms;       /* wall time of the call incl. copies */
-	uint64_t reserved[4];
+	/* walk efficiency of the direct-light loop (instrumented instance): warp-level NODE / PRIM steps taken,
+	 * the lanes that took part in them, and the lanes that had no shadow ray at the time (waiting for a
+	 * refill); 32 * steps - lanes - idle = lanes whose ray only had work of the other kind */
+	uint64_t node_steps, node_step_lanes, node_step_idle;
+	uint64_t prim_steps, prim_step_lanes, prim_step_idle;
 } crt_stats;
 
 typedef struct crt_scene crt_scene; /* opaque; owns all device memory */
