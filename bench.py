@@ -13,11 +13,13 @@ reference; the count of one frame is a pure function of (scene,
 options, seed) -- it is taken once, before timing, from the instrumented kernel
 instance, and is identical to the reference's own count (tests/test_gpu_parity).
 
-N > 1 (torchrun, one process per GPU): the scene is replicated, the frame is
-cut into 8x4-pixel tiles dealt round-robin to the
-ranks (crt_render_opts.shard_*), and the framebuffer is assembled on rank 0
-with one NCCL reduce(sum) of the disjoint, zero-elsewhere shards over NVLink.
-Total work is fixed, so scaling is "strong".
+N > 1 (torchrun, one process per GPU): the scene is replicated and ALL ranks
+drain one work queue (crt_frame_share, include/crt.h): frame and work counter
+live on rank 0's GPU, mapped into the other processes by CUDA IPC over NVLink;
+every resident warp of every GPU pulls the next 8-pixel unit with a
+system-scope atomic and writes its pixels straight into rank 0's frame -- dynamic
+load balance, no assembly step.  (--static-shards: the round-1 path, tiles dealt
+round-robin + NCCL reduce.)  Total work is fixed, so scaling is "strong".
 
 --impl reference times the UNMODIFIED reference (oracle/_ref/engine_ref, built
 from /root/reference with its release flags and the thread-local RNG patch) on
@@ -37,7 +39,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-SAMPLE_W, SAMPLE_H = 96, 54  # CPU-baseline sample: the same view at 1/400 of the pixels
+SAMPLE_W, SAMPLE_H = 320, 180  # CPU-baseline sample: the same view at 1/36 of the pixels (>= 5 rows per thread on 32 cores)
 
 
 def parse_args():
@@ -52,12 +54,27 @@ def parse_args():
     ap.add_argument("--spp", type=int, default=16, help="-n: GI samples at the primary hit")
     ap.add_argument("--gi", default="path", choices=["path", "ambient"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--static-shards", action="store_true", help="N > 1: static tile shards + NCCL reduce instead of the shared work queue")
     ap.add_argument("--sample", default=f"{SAMPLE_W}x{SAMPLE_H}", help="frame size of the CPU-baseline sample")
+    ap.add_argument("--ref-steps", type=int, default=1, help="--impl reference: timed runs of the sample (each is all host cores for tens of seconds)")
+    ap.add_argument("--ref-warmup", action="store_true", help="--impl reference: one untimed run first")
     return ap.parse_args()
 
 
 def workload_name(a):
     return f"scenes/{a.scene}.json {a.width}x{a.height} -g {a.gi} -n {a.spp} (defaults: -b 10 -a 0.01 -s phong -l sqr)"
+
+
+def metric_name(a):
+    what = {"scene5": "scene5 dragon", "scene6": "scene6 Menger sponge"}.get(a.scene, a.scene)
+    res = {(1920, 1080): "1080p", (3840, 2160): "2160p"}.get((a.width, a.height), f"{a.width}x{a.height}")
+    return f"Mrays/s ({what} {res} {'path-traced' if a.gi == 'path' else 'ambient'})"
+
+
+def geometry_name(a, prims=None):
+    mesh = {"scene5": "stand-in dragon.stl", "scene6": "stand-in menger_sponge.stl"}.get(a.scene)
+    base = f"{mesh} (tools/gen_meshes.py)" if mesh else "the scene file's own geometry"
+    return base if prims is None else f"{base}, {prims} bounded primitives"
 
 
 def engine_flags(a):
@@ -128,14 +145,28 @@ def run_reference_sample(a, sample_w, sample_h):
     if not os.path.exists(oracle.ENGINE_REF) or not os.path.exists(oracle.REF_ENGINE):
         raise RuntimeError("oracle/_ref is missing: run __graft_entry__.build() where /root/reference exists")
     scene = os.path.join("scenes", a.scene + ".json")
+    # torchrun exports OMP_NUM_THREADS=1: the reference's -m max (system.c:54-74) must see the box's cores
+    for k in ("OMP_NUM_THREADS", "OMP_PROC_BIND", "OMP_PLACES", "GOMP_CPU_AFFINITY"):
+        os.environ.pop(k, None)  # also for oracle.ref_render below
+    env = dict(os.environ)
+    try:
+        os.sched_setaffinity(0, range(os.cpu_count()))  # a launcher may also have pinned this process to one core
+    except (AttributeError, OSError):
+        pass
     with tempfile.TemporaryDirectory() as d:
         out = subprocess.run([oracle.ENGINE_REF, scene, os.path.join(d, "o.tif"), str(sample_w), str(sample_h), "-m", "max",
-                              "-p", "real", "-f"] + engine_flags(a), cwd=ROOT, check=True, capture_output=True, text=True).stdout
+                              "-p", "real", "-f"] + engine_flags(a), cwd=ROOT, check=True, capture_output=True, text=True, env=env).stdout
         cores = int(re.search(r"Using (\d+) threads", out).group(1))
         t_start = float(re.search(r"\[(\d+\.\d+)\].*Commencing raytracing", out).group(1))
         t_end = float(re.search(r"\[(\d+\.\d+)\].*Saving image", out).group(1))
-        _, _, cnt = oracle.ref_render(scene, sample_w, sample_h, engine_flags(a), seed=1)
-    return cnt["cast_ray"] + cnt["shadow"], t_end - t_start, cores
+        key = (a.scene, sample_w, sample_h, tuple(engine_flags(a)))
+        if key not in _RAY_COUNTS:  # a pure function of (scene, size, flags, seed): counted once
+            _, _, cnt = oracle.ref_render(scene, sample_w, sample_h, engine_flags(a), seed=1)
+            _RAY_COUNTS[key] = cnt["cast_ray"] + cnt["shadow"]
+    return _RAY_COUNTS[key], t_end - t_start, cores
+
+
+_RAY_COUNTS = {}
 
 
 def reference_arm(a):
@@ -143,23 +174,28 @@ def reference_arm(a):
     if rank != 0:
         return 0
     sw, sh = (int(x) for x in a.sample.split("x"))
-    for _ in range(min(a.warmup, 1)):
+    # one run of the sample is 20 .. 60 s of all host cores: a single warm-up-free run unless asked otherwise
+    warm = 1 if a.ref_warmup else 0
+    for _ in range(warm):
         run_reference_sample(a, sw, sh)
     rays = secs = 0.0
     cores = 0
-    steps = max(1, min(a.steps, 3))
+    steps = max(1, min(a.steps, a.ref_steps))
     for _ in range(steps):
         r, s, cores = run_reference_sample(a, sw, sh)
         rays += r
         secs += s
     mrays = rays / secs / 1e6
-    sample = (f"{a.scene} at {sw}x{sh} (same view, 1/{(a.width * a.height) // (sw * sh)} of the pixels), same flags; "
-              f"reference render() timed by its own log, {steps} runs")
+    full = a.width * a.height
+    sample = (f"{a.scene} at {sw}x{sh} (same view, 1/{full // (sw * sh)} of the pixels, {sh} rows over {cores} threads), same flags; "
+              f"reference render() timed by its own log, {steps} run(s); a full {a.width}x{a.height} frame would take "
+              f"{secs / steps * full / (sw * sh):.0f} s at this rate")
     line = {
-        "impl": "reference", "metric": "Mrays/s (scene5 dragon 1080p path-traced)", "value": mrays, "unit": "Mrays/s",
-        "n_gpus": a.gpus, "steps": steps, "warmup": min(a.warmup, 1), "ms_per_step": secs / steps * 1e3,
+        "impl": "reference", "metric": metric_name(a), "value": mrays, "unit": "Mrays/s",
+        "n_gpus": a.gpus, "steps": steps, "warmup": warm, "ms_per_step": secs / steps * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(a), "geometry": "stand-in dragon.stl (tools/gen_meshes.py)"},
+        "config": {"workload": workload_name(a), "geometry": geometry_name(a), "sample": f"{sw}x{sh}",
+                   "same_config": sw == a.width and sh == a.height, "host_cores": os.cpu_count(), "threads": cores},
         "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -201,12 +237,17 @@ def ours(a):
     W, H = a.width, a.height
     pixels = W * H
 
+    dynamic = world > 1 and not a.static_shards
+
     def make_opts(count=False):
         o = scene.options(W, H, *engine_flags(a))
-        multigpu.shard_options(o, rank, world)
+        if not dynamic:
+            multigpu.shard_options(o, rank, world)
         if count:
             o.flags |= _abi.CRT_RENDER_COUNT_STATS
         return o
+
+    shared = multigpu.SharedFrame(dev, make_opts(), local) if dynamic else None
 
     d_raster = torch.empty((H, W, 3), dtype=torch.float32, device="cuda")
     d_z = torch.empty((H, W), dtype=torch.float32, device="cuda")
@@ -215,8 +256,13 @@ def ours(a):
 
     # ---- one instrumented frame: ray and test counts (untimed) --------------------
     st = _abi.Stats()
-    dev.render_device(make_opts(count=True), d_raster.data_ptr(), d_z.data_ptr(), stream.cuda_stream)
+    if dynamic:
+        shared.render(dev, make_opts(count=True))
+    else:
+        dev.render_device(make_opts(count=True), d_raster.data_ptr(), d_z.data_ptr(), stream.cuda_stream)
     dev.sync(st)
+    if dynamic:
+        shared.complete()
     counts = torch.tensor([st.rays_closest, st.rays_shadow, st.box_tests, *st.tri_tests, *st.sphere_tests, st.plane_tests],
                           dtype=torch.float64, device="cuda")
     flops_local = _abi.algorithmic_flops(st)
@@ -238,6 +284,12 @@ def ours(a):
     def step_device():
         """one frame, framebuffer left on rank 0's device"""
         flush.zero_()  # L2 flush between steps (outside the kernel's own events)
+        if dynamic:
+            shared.render(dev, opts)  # all ranks drain one work queue, pixels go straight to rank 0's frame
+            ev_a0.record()
+            shared.complete()         # one-element all-reduce: every rank's kernel has finished
+            ev_a1.record()
+            return
         dev.render_device(opts, d_raster.data_ptr(), d_z.data_ptr(), stream.cuda_stream)
         if world > 1:
             ev_a0.record()
@@ -290,7 +342,10 @@ def ours(a):
         barrier()
         ev_a0.record()
         for _ in range(5):
-            multigpu.assemble(d_raster, d_z, 0)
+            if dynamic:
+                shared.complete()
+            else:
+                multigpu.assemble(d_raster, d_z, 0)
         ev_a1.record()
         torch.cuda.synchronize()
         assemble_alone_ms = ev_a0.elapsed_time(ev_a1) / 5.0
@@ -309,8 +364,8 @@ def ours(a):
         else:
             step_device()
             if rank == 0:
-                h_raster.copy_(d_raster, non_blocking=True)
-                h_z.copy_(d_z, non_blocking=True)
+                h_raster.copy_(shared.raster if dynamic else d_raster, non_blocking=True)
+                h_z.copy_(shared.z if dynamic else d_z, non_blocking=True)
             torch.cuda.synchronize()
 
     for _ in range(min(a.warmup, 2)):
@@ -338,8 +393,11 @@ def ours(a):
     # DRAM bytes per launch of this kernel from the committed ncu capture of this very workload (not measured live)
     traffic = None
     try:
+        import hashlib
         t = json.load(open(os.path.join(ROOT, "profiles", "dram_traffic.json")))
-        if t["workload"] == workload_name(a) and world == t["n_gpus"]:
+        sha = hashlib.sha256(open(device.LIB_PATH, "rb").read()).hexdigest()
+        # only the capture of THIS build of libcrt.so on THIS workload counts
+        if t["workload"] == workload_name(a) and world == t["n_gpus"] and t.get("libcrt_sha256") == sha:
             traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     except (OSError, KeyError, ValueError):
         pass
@@ -350,18 +408,20 @@ def ours(a):
         "peak_source": "measured live: crt_measure_fp32_peak (FFMA micro-kernel); nominal 148*128*2*1.965 GHz = 74.4",
         "flops_per_ray": total_flops / total_rays, "box_tests_per_ray": tot.box_tests / total_rays,
         "note": "algorithmic FLOPs by SURVEY 8(d): 3/ray + 12/box test + tri 14/24/40/46 + sphere 17/20 + plane 12; "
-                "HBM is not the bound (scene %.0f MB mostly L2-resident; traffic = DRAM bytes per launch from profiles/dram_traffic.json, "
-                "about 20 GB/s against the measured hbm peak of %s GB/s)" % (info.device_bytes / 1e6, peaks.get("hbm_gbs")),
+                "HBM is not the bound (scene %.0f MB mostly L2-resident; traffic = DRAM bytes per launch from profiles/dram_traffic.json "
+                "when it was captured from this build of libcrt.so, else null; measured hbm peak %s GB/s)" % (info.device_bytes / 1e6, peaks.get("hbm_gbs")),
     }
 
     line = {
-        "metric": "Mrays/s (scene5 dragon 1080p path-traced)", "value": value, "unit": "Mrays/s",
+        "metric": metric_name(a), "value": value, "unit": "Mrays/s",
         "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {
-            "workload": workload_name(a), "geometry": "stand-in dragon.stl, %d bounded primitives (tools/gen_meshes.py)" % info.num_bounded,
+            "workload": workload_name(a), "geometry": geometry_name(a, info.num_bounded),
             "rays_per_frame": total_rays, "rays_closest": tot.rays_closest, "rays_shadow": tot.rays_shadow,
-            "l2": "flushed between steps (256 MiB memset)", "parallelism": f"tile-chunk round-robin x{world}, scene replicated",
+            "l2": "flushed between steps (256 MiB memset)", "parallelism": (f"one dynamic work queue over {world} GPUs (crt_frame_share: 8-pixel units, system-scope atomics, "
+                                                                          f"frame on rank 0 over CUDA IPC / NVLink), scene replicated" if dynamic else
+                                                                          f"tile-chunk round-robin x{world}, scene replicated"),
             "bvh_nodes": info.num_nodes, "bvh_build_ms": info.build_ms, "scene_upload_ms": info.upload_ms,
             "scene_setup_s": setup_s, "seed": 1, "assemble_ms": assemble_ms, "assemble_alone_ms": assemble_alone_ms,
             "per_rank_ms": per_rank_ms,
@@ -369,7 +429,8 @@ def ours(a):
         "ms_per_frame": ms_per_step,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_frame": float(e2e_ms[0]),
                 "h2d_bytes_per_step": C.sizeof(_abi.RenderOpts), "d2h_bytes_per_step": 16 * pixels,
-                "note": "crt_render() with host buffers, scene resident (the reference's render() seam); "
+                "note": ("crt_render() with host buffers, scene resident (the reference's render() seam); " if world == 1 else
+                         "crt_render_device_shared() on every rank + D2H of the finished frame from rank 0's GPU to pinned host memory; ") +
                         "scene build+upload is config.scene_setup_s, once per scene"},
         "gpu_launches": 2 * a.steps,
         "clocks": clocks,
@@ -379,13 +440,23 @@ def ours(a):
 
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         sw, sh = (int(x) for x in a.sample.split("x"))
+        # rays of the sample frame: counted by the instrumented kernel instance (equal to the reference's own
+        # count, tests/test_gpu_parity.py) -- saves a second, instrumented, run of the reference
+        so = scene.options(sw, sh, *engine_flags(a))
+        so.flags |= _abi.CRT_RENDER_COUNT_STATS
+        sst = _abi.Stats()
+        dev.render(so, sst)
+        _RAY_COUNTS[(a.scene, sw, sh, tuple(engine_flags(a)))] = sst.rays_closest + sst.rays_shadow
         rays, secs, cores = run_reference_sample(a, sw, sh)
         line["cpu_baseline"] = {
             "value": rays / secs / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "reference",
-            "sample": f"{a.scene} at {sw}x{sh} (same view, 1/{pixels // (sw * sh)} of the pixels), same flags, "
+            "host_cores": os.cpu_count(),
+            "sample": f"{a.scene} at {sw}x{sh} (same view, 1/{pixels // (sw * sh)} of the pixels, {sh} rows over {cores} threads), same flags, "
                       f"{rays} rays in {secs:.2f} s; oracle/_ref/engine_ref = unmodified reference, -Ofast -fopenmp, -m max, thread-local RNG"}
     if rank == 0:
         print(json.dumps(line))
+    if shared is not None:
+        shared.close()
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -84,6 +84,10 @@ class Stats(C.Structure):
         }
 
 
+class FrameShare(C.Structure):
+    _fields_ = [("work_counter", C.c_void_p), ("total_warps", C.c_uint32), ("reserved", C.c_uint32 * 5)]
+
+
 class SceneInfo(C.Structure):
     _fields_ = [
         ("num_bounded", C.c_uint32), ("num_planes", C.c_uint32), ("num_emitters", C.c_uint32),

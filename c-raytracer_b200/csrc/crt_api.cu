@@ -203,47 +203,45 @@ void crt_scene_destroy(crt_scene *s)
 	delete s;
 }
 
-int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
+/* The scene as the device wants it, built once on the host (accel_init(), accel.c:266-315) and
+ * uploaded to one or several devices. */
+struct HostScene {
+	std::vector<float4> wide_nodes, prims, planes;
+	std::vector<int32_t> obj_slot, slot_object;
+	std::vector<DEmitter> emitters;
+	std::vector<crt_material> mats;
+	uint32_t num_objects = 0, num_bounded = 0, total_lights = 0, wide_nodes_count = 0, wide_depth = 0;
+	float ambient[3] = { 0.f, 0.f, 0.f };
+	double build_ms = 0.0;
+};
+
+static int build_host_scene(const crt_scene_desc *desc, HostScene &h)
 {
-	if (!out)
-		return fail(CRT_ERR_INVALID, "out is NULL");
-	*out = nullptr;
 	int rc = validate(desc);
 	if (rc)
 		return rc;
-	rc = ensure_device(device);
-	if (rc)
-		return rc;
-
-	crt_scene *s = new crt_scene();
-	s->device = device;
-	s->num_materials = desc->num_materials;
-	cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
 
 	/* ---- materials ------------------------------------------------------ */
-	std::vector<crt_material> mats(desc->materials, desc->materials + desc->num_materials);
-	for (auto &m : mats)
+	h.mats.assign(desc->materials, desc->materials + desc->num_materials);
+	for (auto &m : h.mats)
 		m.flags = material_flags(m);
+	const std::vector<crt_material> &mats = h.mats;
 
 	/* ---- split objects: planes (linear list, object.c:168-197) / bounded --- */
 	const uint32_t n = desc->num_objects;
 	std::vector<uint32_t> bounded;
-	std::vector<float4> planes;
-	std::vector<int32_t> obj_slot(n, 0);
-	std::vector<DEmitter> emitters;
+	h.obj_slot.assign(n, 0);
 	uint32_t total_lights = 0;
 	for (uint32_t i = 0; i < n; i++) {
 		const crt_object &o = desc->objects[i];
 		const crt_material &m = mats[o.material];
 		const uint32_t info = static_cast<uint32_t>(o.material) | ((m.flags & CRT_MAT_TRANSPARENT) ? PRIM_TRANSPARENT : 0u);
 		if (o.type == CRT_OBJ_PLANE) {
-			if (m.flags & CRT_MAT_EMITTANT) {
-				delete s;
+			if (m.flags & CRT_MAT_EMITTANT)
 				return fail(CRT_ERR_INVALID, "Plane cannot be emittant");
-			}
-			obj_slot[i] = ~static_cast<int32_t>(planes.size() / 2);
-			planes.push_back(make_float4(o.a[0], o.a[1], o.a[2], o.b[0]));
-			planes.push_back(make_float4(o.epsilon, as_float(info), as_float(i), 0.f));
+			h.obj_slot[i] = ~static_cast<int32_t>(h.planes.size() / 2);
+			h.planes.push_back(make_float4(o.a[0], o.a[1], o.a[2], o.b[0]));
+			h.planes.push_back(make_float4(o.epsilon, as_float(info), as_float(i), 0.f));
 			continue;
 		}
 		bounded.push_back(i);
@@ -266,12 +264,10 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 			const float inv = o.num_lights ? 1.f / static_cast<float>(o.num_lights) : 0.f;
 			for (int k = 0; k < 3; k++)
 				e.ke_n[k] = m.ke[k] * inv;
-			if (static_cast<uint64_t>(total_lights) + o.num_lights > kMaxLights) {
-				delete s;
+			if (static_cast<uint64_t>(total_lights) + o.num_lights > kMaxLights)
 				return fail(CRT_ERR_INVALID, "more than %u light samples in the scene", kMaxLights);
-			}
 			total_lights += o.num_lights;
-			emitters.push_back(e);
+			h.emitters.push_back(e);
 		}
 	}
 
@@ -301,50 +297,65 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 	/* the device tree: 8-wide collapse of the binary tree, one primitive per leaf slot, half-precision child boxes */
 	WideTree wide;
 	build_wide(boxes, bvh, wide);
-	if (wide.max_depth > kWideMaxDepth || wide.nodes.size() > kWideMaxNodes || bounded.size() > kWideMaxPrims) {
-		delete s;
+	if (wide.max_depth > kWideMaxDepth || wide.nodes.size() > kWideMaxNodes || bounded.size() > kWideMaxPrims)
 		return fail(CRT_ERR_UNSUPPORTED, "scene too large for the device tree (%zu nodes, %zu primitives, %u levels)",
 			wide.nodes.size(), bounded.size(), wide.max_depth);
-	}
-	s->info.build_ms = now_ms() - t0;
+	h.build_ms = now_ms() - t0;
 
 	/* ---- primitive records in the order of the wide tree -------------------- */
-	const double t1 = now_ms();
-	std::vector<float4> prims(4 * bounded.size());
-	s->slot_object.resize(bounded.size());
+	h.prims.resize(4 * bounded.size());
+	h.slot_object.resize(bounded.size());
 	for (size_t slot = 0; slot < bounded.size(); slot++) {
 		const uint32_t oi = bounded[wide.order[slot]];
 		const crt_object &o = desc->objects[oi];
 		const crt_material &m = mats[o.material];
 		uint32_t info = static_cast<uint32_t>(o.material) | ((m.flags & CRT_MAT_TRANSPARENT) ? PRIM_TRANSPARENT : 0u);
-		obj_slot[oi] = static_cast<int32_t>(slot);
-		s->slot_object[slot] = static_cast<int32_t>(oi);
+		h.obj_slot[oi] = static_cast<int32_t>(slot);
+		h.slot_object[slot] = static_cast<int32_t>(oi);
 		if (o.type == CRT_OBJ_SPHERE) {
 			info |= PRIM_SPHERE;
-			prims[4 * slot + 0] = make_float4(o.a[0], o.a[1], o.a[2], o.epsilon);
-			prims[4 * slot + 1] = make_float4(o.b[0], 0.f, 0.f, as_float(info));
-			prims[4 * slot + 2] = make_float4(0.f, 0.f, 0.f, as_float(oi));
-			prims[4 * slot + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
+			h.prims[4 * slot + 0] = make_float4(o.a[0], o.a[1], o.a[2], o.epsilon);
+			h.prims[4 * slot + 1] = make_float4(o.b[0], 0.f, 0.f, as_float(info));
+			h.prims[4 * slot + 2] = make_float4(0.f, 0.f, 0.f, as_float(oi));
+			h.prims[4 * slot + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
 		} else {
-			prims[4 * slot + 0] = make_float4(o.a[0], o.a[1], o.a[2], o.epsilon);
-			prims[4 * slot + 1] = make_float4(o.b[0], o.b[1], o.b[2], as_float(info));
-			prims[4 * slot + 2] = make_float4(o.c[0], o.c[1], o.c[2], as_float(oi));
-			prims[4 * slot + 3] = make_float4(o.n[0], o.n[1], o.n[2], 0.f);
+			h.prims[4 * slot + 0] = make_float4(o.a[0], o.a[1], o.a[2], o.epsilon);
+			h.prims[4 * slot + 1] = make_float4(o.b[0], o.b[1], o.b[2], as_float(info));
+			h.prims[4 * slot + 2] = make_float4(o.c[0], o.c[1], o.c[2], as_float(oi));
+			h.prims[4 * slot + 3] = make_float4(o.n[0], o.n[1], o.n[2], 0.f);
 		}
 	}
-
-	/* ---- upload -------------------------------------------------------------- */
-	std::vector<float4> wide_nodes(8 * wide.nodes.size());
+	h.wide_nodes.resize(8 * wide.nodes.size());
 	if (!wide.nodes.empty())
-		std::memcpy(wide_nodes.data(), wide.nodes.data(), wide.nodes.size() * sizeof(WideNode));
-	rc = CRT_OK;
-	if (!rc) rc = upload(s, wide_nodes, &s->d.wide);
-	s->wide_bytes = wide_nodes.size() * sizeof(float4);
-	if (!rc) rc = upload(s, prims, &s->d.prims);
-	if (!rc) rc = upload(s, planes, &s->d.planes);
-	if (!rc) rc = upload(s, obj_slot, &s->d.obj_slot);
-	if (!rc) rc = upload(s, emitters, &s->d.emitters);
-	if (!rc) rc = upload(s, mats, &s->d.materials);
+		std::memcpy(h.wide_nodes.data(), wide.nodes.data(), wide.nodes.size() * sizeof(WideNode));
+	h.num_objects = n;
+	h.num_bounded = static_cast<uint32_t>(bounded.size());
+	h.total_lights = total_lights;
+	h.wide_nodes_count = static_cast<uint32_t>(wide.nodes.size());
+	h.wide_depth = wide.max_depth;
+	std::memcpy(h.ambient, desc->ambient, sizeof h.ambient);
+	return CRT_OK;
+}
+
+/* plain H2D copies of a built scene onto `device` */
+static int upload_host_scene(const HostScene &h, int device, crt_scene **out)
+{
+	int rc = ensure_device(device);
+	if (rc)
+		return rc;
+	const double t1 = now_ms();
+	crt_scene *s = new crt_scene();
+	s->device = device;
+	s->num_materials = static_cast<uint32_t>(h.mats.size());
+	s->slot_object = h.slot_object;
+	cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
+	rc = upload(s, h.wide_nodes, &s->d.wide);
+	s->wide_bytes = h.wide_nodes.size() * sizeof(float4);
+	if (!rc) rc = upload(s, h.prims, &s->d.prims);
+	if (!rc) rc = upload(s, h.planes, &s->d.planes);
+	if (!rc) rc = upload(s, h.obj_slot, &s->d.obj_slot);
+	if (!rc) rc = upload(s, h.emitters, &s->d.emitters);
+	if (!rc) rc = upload(s, h.mats, &s->d.materials);
 	if (!rc && cudaMalloc(&s->tile_counter, sizeof(unsigned int)) != cudaSuccess)
 		rc = fail(CRT_ERR_CUDA, "cudaMalloc(tile counter) failed");
 	if (!rc && cudaMalloc(&s->counters, kNumCounters * sizeof(unsigned long long)) != cudaSuccess)
@@ -355,26 +366,45 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 		crt_scene_destroy(s);
 		return rc;
 	}
-	s->d.num_nodes = static_cast<uint32_t>(wide.nodes.size());
-	s->wide_depth = wide.max_depth;
-	s->d.num_prims = static_cast<uint32_t>(bounded.size());
-	s->d.num_planes = static_cast<uint32_t>(planes.size() / 2);
-	s->d.num_emitters = static_cast<uint32_t>(emitters.size());
-	s->d.num_objects = n;
-	s->d.total_lights = total_lights;
-	std::memcpy(s->d.ambient, desc->ambient, sizeof s->d.ambient);
+	s->d.num_nodes = h.wide_nodes_count;
+	s->wide_depth = h.wide_depth;
+	s->d.num_prims = h.num_bounded;
+	s->d.num_planes = static_cast<uint32_t>(h.planes.size() / 2);
+	s->d.num_emitters = static_cast<uint32_t>(h.emitters.size());
+	s->d.num_objects = h.num_objects;
+	s->d.total_lights = h.total_lights;
+	std::memcpy(s->d.ambient, h.ambient, sizeof s->d.ambient);
 
+	s->info.build_ms = h.build_ms;
 	s->info.upload_ms = now_ms() - t1;
 	s->info.num_bounded = s->d.num_prims;
 	s->info.num_planes = s->d.num_planes;
 	s->info.num_emitters = s->d.num_emitters;
-	s->info.total_lights = total_lights;
+	s->info.total_lights = h.total_lights;
 	s->info.num_nodes = s->d.num_nodes;
-	s->info.max_depth = wide.max_depth;
+	s->info.max_depth = h.wide_depth;
 	s->info.device = static_cast<uint32_t>(device);
 	s->info.sm_count = static_cast<uint32_t>(s->sm_count);
 	*out = s;
 	return CRT_OK;
+}
+
+int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
+{
+	if (!out)
+		return fail(CRT_ERR_INVALID, "out is NULL");
+	*out = nullptr;
+	int rc = validate(desc);
+	if (rc)
+		return rc;
+	rc = ensure_device(device);
+	if (rc)
+		return rc;
+	HostScene h;
+	rc = build_host_scene(desc, h);
+	if (rc)
+		return rc;
+	return upload_host_scene(h, device, out);
 }
 
 int crt_scene_get_info(const crt_scene *s, crt_scene_info *info)
@@ -387,8 +417,28 @@ int crt_scene_get_info(const crt_scene *s, crt_scene_info *info)
 
 int crt_render_device(crt_scene *s, const crt_render_opts *opts, float *d_raster, float *d_z, void *cuda_stream)
 {
+	return crt_render_device_shared(s, opts, d_raster, d_z, cuda_stream, nullptr);
+}
+
+int crt_scene_resident_warps(crt_scene *s, const crt_render_opts *opts, uint32_t *warps)
+{
+	if (!s || !warps)
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	CUDA_TRY(cudaSetDevice(s->device));
+	const int per_sm = render_blocks_per_sm(opts && (opts->flags & CRT_RENDER_COUNT_STATS));
+	if (per_sm <= 0)
+		return fail(CRT_ERR_CUDA, "render kernel cannot be resident (%s)", cudaGetErrorString(cudaGetLastError()));
+	*warps = static_cast<uint32_t>(per_sm * s->sm_count * kWarpsPerBlock);
+	return CRT_OK;
+}
+
+int crt_render_device_shared(crt_scene *s, const crt_render_opts *opts, float *d_raster, float *d_z, void *cuda_stream,
+	const crt_frame_share *share)
+{
 	if (!s || !opts || !d_raster || !d_z)
 		return fail(CRT_ERR_INVALID, "NULL argument");
+	if (share && (!share->work_counter || !share->total_warps || opts->shard_count != 1u))
+		return fail(CRT_ERR_INVALID, "shared frame: needs a work counter, the total warp count and an unsharded frame");
 	if (!opts->width || !opts->height)
 		return fail(CRT_ERR_INVALID, "empty image");
 	if (!opts->shard_count || opts->shard_index >= opts->shard_count)
@@ -461,7 +511,8 @@ int crt_render_device(crt_scene *s, const crt_render_opts *opts, float *d_raster
 	/* tiles from fine_from on are handed out as quarter tiles (one 8-pixel row per warp): bounds
 	 * the tail of the persistent grid and keeps a warp's shading points close together */
 	{
-		const uint32_t warps = static_cast<uint32_t>(grid) * kWarpsPerBlock;
+		/* a shared frame is drained by the resident warps of every participant */
+		const uint32_t warps = share ? share->total_warps : static_cast<uint32_t>(grid) * kWarpsPerBlock;
 		uint32_t fine = p.num_local_tiles; /* measured: quarter tiles throughout are never slower (profiles/) */
 		if (const char *e = std::getenv("CRT_FINE_PERCENT"))
 			fine = static_cast<uint32_t>(static_cast<uint64_t>(p.num_local_tiles) * std::min(100, std::max(0, std::atoi(e))) / 100u);
@@ -481,7 +532,8 @@ int crt_render_device(crt_scene *s, const crt_render_opts *opts, float *d_raster
 		p.micro_from = p.fine_from + (fine - micro_tiles) * kTileH;
 		p.num_units = p.micro_from + micro_tiles * (tile_pixels / micro_pixels);
 	}
-	p.tile_counter = s->tile_counter;
+	p.tile_counter = share ? share->work_counter : s->tile_counter;
+	p.system_counter = share ? 1u : 0u;
 	p.counters = s->counters;
 	p.pending = s->pending;
 	p.slots = s->pending + (pending_floats - slots_floats);
@@ -505,11 +557,14 @@ int crt_render_device(crt_scene *s, const crt_render_opts *opts, float *d_raster
 		}
 	}
 
-	CUDA_TRY(cudaMemsetAsync(s->tile_counter, 0, sizeof(unsigned int), stream));
+	if (!share)
+		CUDA_TRY(cudaMemsetAsync(s->tile_counter, 0, sizeof(unsigned int), stream));
 	CUDA_TRY(cudaMemsetAsync(s->counters, 0, kNumCounters * sizeof(unsigned long long), stream));
 	/* pixels of other shards (and misses) are zero: the reference relies on fresh zero pages */
-	CUDA_TRY(cudaMemsetAsync(d_raster, 0, 3 * pixels * sizeof(float), stream));
-	CUDA_TRY(cudaMemsetAsync(d_z, 0, pixels * sizeof(float), stream));
+	if (!share) { /* the participants of a shared frame write every pixel between them */
+		CUDA_TRY(cudaMemsetAsync(d_raster, 0, 3 * pixels * sizeof(float), stream));
+		CUDA_TRY(cudaMemsetAsync(d_z, 0, pixels * sizeof(float), stream));
+	}
 	CUDA_TRY(cudaEventRecord(s->ev_start, stream));
 	launch_raygen_rows(*opts, s->row_pos, stream);
 	launch_render(p, grid, count, stream);
@@ -586,6 +641,317 @@ int crt_render(crt_scene *s, const crt_render_opts *opts, float *raster, float *
 	CUDA_TRY(cudaMemcpy(z_buffer, s->d_z, pixels * sizeof(float), cudaMemcpyDeviceToHost));
 	if (stats)
 		stats->total_ms = now_ms() - t0;
+	return CRT_OK;
+}
+
+/* ---- several devices, one frame (crt_multi) -------------------------------------- */
+
+struct crt_multi {
+	std::vector<crt_scene *> scenes;
+	std::vector<cudaStream_t> streams;
+	bool dynamic = false;          /* shared work queue + frame on scenes[0]'s device over peer access */
+	unsigned int *work_counter = nullptr; /* on scenes[0]'s device */
+	float *h_raster = nullptr, *h_z = nullptr; /* static mode: pinned staging, one frame per device */
+	size_t h_pixels = 0;
+};
+
+void crt_multi_destroy(crt_multi *m)
+{
+	if (!m)
+		return;
+	for (size_t k = 0; k < m->scenes.size(); k++) {
+		if (m->scenes[k]) {
+			cudaSetDevice(m->scenes[k]->device);
+			if (k < m->streams.size() && m->streams[k])
+				cudaStreamDestroy(m->streams[k]);
+		}
+	}
+	if (!m->scenes.empty() && m->scenes[0]) {
+		cudaSetDevice(m->scenes[0]->device);
+		cudaFree(m->work_counter);
+	}
+	cudaFreeHost(m->h_raster);
+	cudaFreeHost(m->h_z);
+	for (crt_scene *sc : m->scenes)
+		crt_scene_destroy(sc);
+	delete m;
+}
+
+int crt_multi_create(const crt_scene_desc *desc, const int *devices, int num_devices, crt_multi **out)
+{
+	if (!out)
+		return fail(CRT_ERR_INVALID, "out is NULL");
+	*out = nullptr;
+	if (!devices || num_devices < 1 || num_devices > 64)
+		return fail(CRT_ERR_INVALID, "bad device list (%d devices)", num_devices);
+	int rc = validate(desc);
+	if (rc)
+		return rc;
+	for (int k = 0; k < num_devices; k++) {
+		rc = ensure_device(devices[k]);
+		if (rc)
+			return rc;
+	}
+	HostScene h;
+	rc = build_host_scene(desc, h); /* once: every device gets the same tree */
+	if (rc)
+		return rc;
+	crt_multi *m = new crt_multi();
+	m->scenes.assign(num_devices, nullptr);
+	m->streams.assign(num_devices, nullptr);
+	for (int k = 0; k < num_devices && !rc; k++) {
+		rc = upload_host_scene(h, devices[k], &m->scenes[k]);
+		if (!rc && cudaStreamCreateWithFlags(&m->streams[k], cudaStreamNonBlocking) != cudaSuccess)
+			rc = fail(CRT_ERR_CUDA, "cudaStreamCreate failed on device %d", devices[k]);
+	}
+	/* peer access of every other device to devices[0] (frame + work counter live there) */
+	bool peers = !rc;
+	for (int k = 1; k < num_devices && peers; k++) {
+		if (devices[k] == devices[0])
+			continue;
+		int can = 0;
+		if (cudaDeviceCanAccessPeer(&can, devices[k], devices[0]) != cudaSuccess || !can) {
+			cudaGetLastError();
+			peers = false;
+			break;
+		}
+		cudaSetDevice(devices[k]);
+		const cudaError_t e = cudaDeviceEnablePeerAccess(devices[0], 0);
+		if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+			peers = false;
+		cudaGetLastError();
+	}
+	if (const char *e = std::getenv("CRT_MULTI_STATIC")) /* force the static-shard path (tests) */
+		if (std::atoi(e))
+			peers = false;
+	m->dynamic = peers;
+	if (!rc && m->dynamic) {
+		cudaSetDevice(devices[0]);
+		if (cudaMalloc(&m->work_counter, sizeof(unsigned int)) != cudaSuccess)
+			rc = fail(CRT_ERR_CUDA, "cudaMalloc(work counter) failed");
+	}
+	if (rc) {
+		crt_multi_destroy(m);
+		return rc;
+	}
+	*out = m;
+	return CRT_OK;
+}
+
+int crt_multi_num_devices(const crt_multi *m)
+{
+	return m ? static_cast<int>(m->scenes.size()) : 0;
+}
+
+int crt_multi_is_dynamic(const crt_multi *m)
+{
+	return m && m->dynamic ? 1 : 0;
+}
+
+int crt_multi_get_info(const crt_multi *m, int index, crt_scene_info *info)
+{
+	if (!m || !info || index < 0 || index >= static_cast<int>(m->scenes.size()))
+		return fail(CRT_ERR_INVALID, "bad argument");
+	*info = m->scenes[index]->info;
+	return CRT_OK;
+}
+
+static void add_stats(crt_stats &acc, const crt_stats &st)
+{
+	acc.rays_closest += st.rays_closest;
+	acc.rays_shadow += st.rays_shadow;
+	acc.box_tests += st.box_tests;
+	for (int i = 0; i < 4; i++)
+		acc.tri_tests[i] += st.tri_tests[i];
+	acc.sphere_tests[0] += st.sphere_tests[0];
+	acc.sphere_tests[1] += st.sphere_tests[1];
+	acc.plane_tests += st.plane_tests;
+	acc.nodes_shaded += st.nodes_shaded;
+	acc.node_steps += st.node_steps;
+	acc.node_step_lanes += st.node_step_lanes;
+	acc.node_step_idle += st.node_step_idle;
+	acc.prim_steps += st.prim_steps;
+	acc.prim_step_lanes += st.prim_step_lanes;
+	acc.prim_step_idle += st.prim_step_idle;
+	acc.kernel_ms = std::fmax(acc.kernel_ms, st.kernel_ms);
+}
+
+int crt_multi_render(crt_multi *m, const crt_render_opts *opts, float *raster, float *z_buffer, crt_stats *stats, double *device_ms)
+{
+	if (!m || !opts || !raster || !z_buffer)
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	if (opts->shard_count != 1u || opts->shard_index != 0u)
+		return fail(CRT_ERR_INVALID, "crt_multi_render shards the frame itself: pass shard 0 of 1");
+	const double t0 = now_ms();
+	const size_t n = m->scenes.size();
+	const size_t pixels = static_cast<size_t>(opts->width) * opts->height;
+	crt_stats total;
+	std::memset(&total, 0, sizeof total);
+	int rc = CRT_OK;
+
+	if (m->dynamic) {
+		/* frame + counter on scenes[0]'s device; everybody pulls units from the one counter */
+		crt_scene *s0 = m->scenes[0];
+		CUDA_TRY(cudaSetDevice(s0->device));
+		if (s0->staging_pixels < pixels) {
+			cudaFree(s0->d_raster);
+			cudaFree(s0->d_z);
+			s0->d_raster = s0->d_z = nullptr;
+			s0->staging_pixels = 0;
+			CUDA_TRY(cudaMalloc(&s0->d_raster, 3 * pixels * sizeof(float)));
+			CUDA_TRY(cudaMalloc(&s0->d_z, pixels * sizeof(float)));
+			s0->staging_pixels = pixels;
+		}
+		crt_frame_share share;
+		std::memset(&share, 0, sizeof share);
+		share.work_counter = m->work_counter;
+		for (size_t k = 0; k < n; k++) {
+			uint32_t w = 0;
+			rc = crt_scene_resident_warps(m->scenes[k], opts, &w);
+			if (rc)
+				return rc;
+			share.total_warps += w;
+		}
+		CUDA_TRY(cudaSetDevice(s0->device));
+		CUDA_TRY(cudaMemset(m->work_counter, 0, sizeof(unsigned int))); /* synchronous: visible before any participant starts */
+		for (size_t k = 0; k < n && !rc; k++)
+			rc = crt_render_device_shared(m->scenes[k], opts, s0->d_raster, s0->d_z, m->streams[k], &share);
+		for (size_t k = 0; k < n; k++) { /* wait for every frame that was enqueued, also after an error */
+			if (!m->scenes[k]->frame_pending)
+				continue;
+			crt_stats st;
+			const int r2 = crt_render_device_sync(m->scenes[k], &st);
+			if (r2 && !rc)
+				rc = r2;
+			if (!r2) {
+				add_stats(total, st);
+				if (device_ms)
+					device_ms[k] = st.kernel_ms;
+			}
+		}
+		if (rc)
+			return rc;
+		CUDA_TRY(cudaSetDevice(s0->device));
+		CUDA_TRY(cudaMemcpy(raster, s0->d_raster, 3 * pixels * sizeof(float), cudaMemcpyDeviceToHost));
+		CUDA_TRY(cudaMemcpy(z_buffer, s0->d_z, pixels * sizeof(float), cudaMemcpyDeviceToHost));
+	} else {
+		/* static shards (tile k -> device k mod n, crt_render_opts.shard_*), merged on the host:
+		 * shards are disjoint and zero elsewhere, so the sum is exact */
+		if (m->h_pixels < pixels * n) {
+			cudaFreeHost(m->h_raster);
+			cudaFreeHost(m->h_z);
+			m->h_raster = m->h_z = nullptr;
+			m->h_pixels = 0;
+			CUDA_TRY(cudaHostAlloc(&m->h_raster, n * 3 * pixels * sizeof(float), cudaHostAllocPortable));
+			CUDA_TRY(cudaHostAlloc(&m->h_z, n * pixels * sizeof(float), cudaHostAllocPortable));
+			m->h_pixels = pixels * n;
+		}
+		for (size_t k = 0; k < n && !rc; k++) {
+			crt_scene *sk = m->scenes[k];
+			CUDA_TRY(cudaSetDevice(sk->device));
+			if (sk->staging_pixels < pixels) {
+				cudaFree(sk->d_raster);
+				cudaFree(sk->d_z);
+				sk->d_raster = sk->d_z = nullptr;
+				sk->staging_pixels = 0;
+				CUDA_TRY(cudaMalloc(&sk->d_raster, 3 * pixels * sizeof(float)));
+				CUDA_TRY(cudaMalloc(&sk->d_z, pixels * sizeof(float)));
+				sk->staging_pixels = pixels;
+			}
+			crt_render_opts o = *opts;
+			o.shard_index = static_cast<uint32_t>(k);
+			o.shard_count = static_cast<uint32_t>(n);
+			rc = crt_render_device_shared(sk, &o, sk->d_raster, sk->d_z, m->streams[k], nullptr);
+			if (!rc) {
+				CUDA_TRY(cudaMemcpyAsync(m->h_raster + k * 3 * pixels, sk->d_raster, 3 * pixels * sizeof(float), cudaMemcpyDeviceToHost, m->streams[k]));
+				CUDA_TRY(cudaMemcpyAsync(m->h_z + k * pixels, sk->d_z, pixels * sizeof(float), cudaMemcpyDeviceToHost, m->streams[k]));
+			}
+		}
+		for (size_t k = 0; k < n; k++) {
+			if (!m->scenes[k]->frame_pending)
+				continue;
+			crt_stats st;
+			const int r2 = crt_render_device_sync(m->scenes[k], &st);
+			if (r2 && !rc)
+				rc = r2;
+			if (!r2) {
+				add_stats(total, st);
+				if (device_ms)
+					device_ms[k] = st.kernel_ms;
+			}
+			cudaSetDevice(m->scenes[k]->device);
+			if (cudaStreamSynchronize(m->streams[k]) != cudaSuccess && !rc)
+				rc = fail(CRT_ERR_CUDA, "copy of shard %zu failed: %s", k, cudaGetErrorString(cudaGetLastError()));
+		}
+		if (rc)
+			return rc;
+		std::memcpy(raster, m->h_raster, 3 * pixels * sizeof(float));
+		std::memcpy(z_buffer, m->h_z, pixels * sizeof(float));
+		for (size_t k = 1; k < n; k++) {
+			const float *r = m->h_raster + k * 3 * pixels, *z = m->h_z + k * pixels;
+			for (size_t i = 0; i < 3 * pixels; i++)
+				raster[i] += r[i];
+			for (size_t i = 0; i < pixels; i++)
+				z_buffer[i] += z[i];
+		}
+	}
+	if (stats) {
+		*stats = total;
+		stats->total_ms = now_ms() - t0;
+	}
+	return CRT_OK;
+}
+
+/* ---- memory shared between processes (one process per GPU) ------------------------ */
+
+int crt_shared_alloc(int device, size_t bytes, void **d_ptr, unsigned char handle[CRT_IPC_HANDLE_BYTES])
+{
+	if (!d_ptr || !handle || !bytes)
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	static_assert(sizeof(cudaIpcMemHandle_t) <= CRT_IPC_HANDLE_BYTES, "IPC handle does not fit");
+	int rc = ensure_device(device);
+	if (rc)
+		return rc;
+	void *p = nullptr;
+	CUDA_TRY(cudaMalloc(&p, bytes));
+	cudaIpcMemHandle_t hnd;
+	const cudaError_t e = cudaIpcGetMemHandle(&hnd, p);
+	if (e != cudaSuccess) {
+		cudaFree(p);
+		return fail(CRT_ERR_CUDA, "cudaIpcGetMemHandle failed: %s", cudaGetErrorString(e));
+	}
+	std::memset(handle, 0, CRT_IPC_HANDLE_BYTES);
+	std::memcpy(handle, &hnd, sizeof hnd);
+	*d_ptr = p;
+	return CRT_OK;
+}
+
+int crt_shared_open(int device, const unsigned char handle[CRT_IPC_HANDLE_BYTES], void **d_ptr)
+{
+	if (!d_ptr || !handle)
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	int rc = ensure_device(device);
+	if (rc)
+		return rc;
+	cudaIpcMemHandle_t hnd;
+	std::memcpy(&hnd, handle, sizeof hnd);
+	void *p = nullptr;
+	CUDA_TRY(cudaIpcOpenMemHandle(&p, hnd, cudaIpcMemLazyEnablePeerAccess));
+	*d_ptr = p;
+	return CRT_OK;
+}
+
+int crt_shared_release(int device, void *d_ptr, int owner)
+{
+	if (!d_ptr)
+		return CRT_OK;
+	int rc = ensure_device(device);
+	if (rc)
+		return rc;
+	if (owner)
+		CUDA_TRY(cudaFree(d_ptr));
+	else
+		CUDA_TRY(cudaIpcCloseMemHandle(d_ptr));
 	return CRT_OK;
 }
 

@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 		 * A pixel's value does not depend on the shape of the unit it is traced in. */
 		uint32_t unit = 0;
 		if (lane == 0)
-			unit = atomicAdd(p.tile_counter, 1u);
+			unit = p.system_counter ? atomicAdd_system(p.tile_counter, 1u) : atomicAdd(p.tile_counter, 1u);
 		unit = __shfl_sync(kFull, unit, 0);
 		if (unit >= p.num_units)
 			break;

@@ -60,6 +60,7 @@ struct RenderParams {
 	uint32_t micro_pixels;          /* 1, 2 or 4 */
 	uint32_t num_units;             /* fine_from tiles + rows of the next tiles + micro units of the last tiles */
 	unsigned int *tile_counter;
+	uint32_t system_counter;        /* the counter is shared with other devices (peer / IPC mapping): system-scope atomics */
 	unsigned long long *counters;   /* kNumCounters, instrumented instance only */
 	float *pending;                 /* per-lane pending-ray stacks */
 	float *slots;                   /* per-warp shadow-ray contribution slots: 3 * kSlots floats each */

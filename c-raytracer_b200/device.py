@@ -18,6 +18,9 @@ SYMBOLS = [
     "crt_last_error", "crt_abi_version", "crt_device_count",
     "crt_scene_create", "crt_scene_destroy", "crt_scene_get_info",
     "crt_render", "crt_render_device", "crt_render_device_sync",
+    "crt_scene_resident_warps", "crt_render_device_shared",
+    "crt_shared_alloc", "crt_shared_open", "crt_shared_release",
+    "crt_multi_create", "crt_multi_destroy", "crt_multi_num_devices", "crt_multi_is_dynamic", "crt_multi_get_info", "crt_multi_render",
     "crt_trace_closest", "crt_trace_shadow", "crt_texture_eval", "crt_measure_fp32_peak",
     "crt_postprocess", "crt_postprocess_device",
 ]
@@ -44,6 +47,18 @@ def lib():
         L.crt_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.crt_render_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.crt_render_device_sync.argtypes = [C.c_void_p, C.c_void_p]
+        L.crt_scene_resident_warps.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]
+        L.crt_render_device_shared.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.crt_shared_alloc.argtypes = [C.c_int, C.c_size_t, C.POINTER(C.c_void_p), C.c_void_p]
+        L.crt_shared_open.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+        L.crt_shared_release.argtypes = [C.c_int, C.c_void_p, C.c_int]
+        L.crt_multi_create.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
+        L.crt_multi_destroy.argtypes = [C.c_void_p]
+        L.crt_multi_destroy.restype = None
+        L.crt_multi_num_devices.argtypes = [C.c_void_p]
+        L.crt_multi_is_dynamic.argtypes = [C.c_void_p]
+        L.crt_multi_get_info.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.crt_multi_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
         L.crt_trace_closest.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
         L.crt_trace_shadow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         L.crt_texture_eval.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_size_t, C.c_void_p]
@@ -131,6 +146,17 @@ class DeviceScene:
     def sync(self, stats=None):
         _check(lib().crt_render_device_sync(self._h, C.addressof(stats) if stats is not None else None))
 
+    def resident_warps(self, opts=None):
+        w = C.c_uint32()
+        _check(lib().crt_scene_resident_warps(self._h, C.addressof(opts) if opts is not None else None, C.byref(w)))
+        return w.value
+
+    def render_device_shared(self, opts, d_raster_ptr, d_z_ptr, stream, share):
+        """crt_render_device_shared: this scene as one participant of a frame several devices / processes render."""
+        _check(lib().crt_render_device_shared(self._h, C.addressof(opts), C.c_void_p(d_raster_ptr), C.c_void_p(d_z_ptr),
+                                              C.c_void_p(stream) if stream else None,
+                                              C.addressof(share) if share is not None else None))
+
     def trace_closest(self, rays):
         rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
         n = len(rays)
@@ -156,3 +182,54 @@ class DeviceScene:
         out = np.zeros_like(pts)
         _check(lib().crt_texture_eval(self._h, material, pts.ctypes.data, len(pts), out.ctypes.data))
         return out
+
+
+def shared_alloc(dev, nbytes):
+    """-> (device pointer, 64-byte IPC handle) of fresh device memory other processes can map"""
+    p = C.c_void_p()
+    h = (C.c_ubyte * 64)()
+    _check(lib().crt_shared_alloc(dev, nbytes, C.byref(p), h))
+    return p.value, bytes(h)
+
+
+def shared_open(dev, handle):
+    p = C.c_void_p()
+    h = (C.c_ubyte * 64).from_buffer_copy(handle)
+    _check(lib().crt_shared_open(dev, h, C.byref(p)))
+    return p.value
+
+
+def shared_release(dev, ptr, owner):
+    _check(lib().crt_shared_release(dev, C.c_void_p(ptr), 1 if owner else 0))
+
+
+class MultiScene:
+    """A scene replicated on several GPUs of this process (crt_multi*): one frame, one dynamic work queue."""
+
+    def __init__(self, scene, devices):
+        self.scene = scene
+        self.devices = list(devices)
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        h = C.c_void_p()
+        _check(lib().crt_multi_create(C.addressof(scene.desc), arr, len(self.devices), C.byref(h)))
+        self._h = h
+        self.dynamic = bool(lib().crt_multi_is_dynamic(self._h))
+        self.info = _abi.SceneInfo()
+        _check(lib().crt_multi_get_info(self._h, 0, C.addressof(self.info)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().crt_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+    def render(self, opts, stats=None, into=None):
+        """crt_multi_render -> (raster, z, per-device kernel ms)"""
+        w, h = opts.width, opts.height
+        raster, z = into if into is not None else (np.empty((h, w, 3), dtype=np.float32), np.empty((h, w), dtype=np.float32))
+        ms = (C.c_double * len(self.devices))()
+        _check(lib().crt_multi_render(self._h, C.addressof(opts), raster.ctypes.data, z.ctypes.data,
+                                      C.addressof(stats) if stats is not None else None, ms))
+        return raster, z, list(ms)

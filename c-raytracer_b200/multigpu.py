@@ -1,4 +1,13 @@
-"""Frame sharding across the GPUs of one node -- one process per GPU.
+"""One frame on the GPUs of one node -- one process per GPU (torchrun).
+
+Two ways, both giving the single-GPU frame bit for bit:
+  SharedFrame      the product path: ONE dynamic work queue over all ranks, frame on rank 0's GPU
+                   mapped into every process (CUDA IPC), no assembly step (include/crt.h
+                   crt_frame_share; within one process the same thing is crt_multi_render);
+  render_sharded   static shards + NCCL reduce (the round-1 path; the fallback where IPC / peer
+                   access is unavailable, and the path the CPU suite runs over gloo).
+
+Static sharding:
 
 The reference parallelises render() over image rows with OpenMP (reference
 src/raytracer/render.c:349-352); pixels are independent and the scene is
@@ -55,3 +64,72 @@ def render_sharded(render, opts, raster, z_buffer, group=None):
     shard_options(opts, rank, world)
     render(opts, raster, z_buffer)
     return assemble(raster, z_buffer, 0, group)
+
+
+class _DevView:
+    """Raw device memory as a CUDA-array-interface object (torch.as_tensor wraps it without a copy)."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"data": (ptr, False), "shape": tuple(shape), "typestr": typestr, "version": 2}
+
+
+class SharedFrame:
+    """One frame rendered by ALL ranks through ONE work queue (crt_frame_share, include/crt.h): frame
+    and work counter live on rank 0's GPU and are mapped into the other processes with CUDA IPC
+    (crt_shared_alloc / crt_shared_open, peer access over NVLink).  Every resident warp of every rank
+    pulls the next 8-pixel unit from the counter and writes its pixels straight into rank 0's
+    frame: load balance is dynamic down to the last unit and there is no assembly step -- the only
+    collectives are two one-element all-reduces per frame that order "counter zeroed" before, and
+    "frame complete" after, the render kernels of all ranks."""
+
+    def __init__(self, dev_scene, opts, local_device, group=None):
+        from . import device as _device
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.local_device = local_device
+        self.width, self.height = opts.width, opts.height
+        pixels = self.width * self.height
+        self.z_offset = 12 * pixels
+        self.counter_offset = (16 * pixels + 255) // 256 * 256
+        nbytes = self.counter_offset + 256
+        box = [None]
+        if self.rank == 0:
+            self.ptr, handle = _device.shared_alloc(local_device, nbytes)
+            box[0] = handle
+        dist.broadcast_object_list(box, src=0, group=group)
+        if self.rank != 0:
+            self.ptr = _device.shared_open(local_device, box[0])
+        warps = torch.tensor([dev_scene.resident_warps(opts)], dtype=torch.int64, device=f"cuda:{local_device}")
+        dist.all_reduce(warps, group=group)
+        from . import _abi
+        self.share = _abi.FrameShare()
+        self.share.work_counter = self.ptr + self.counter_offset
+        self.share.total_warps = int(warps.item())
+        self.token = torch.zeros(1, dtype=torch.int32, device=f"cuda:{local_device}")
+        self.raster = self.z = self.counter = None
+        if self.rank == 0:
+            self.raster = torch.as_tensor(_DevView(self.ptr, (self.height, self.width, 3), "<f4"), device=f"cuda:{local_device}")
+            self.z = torch.as_tensor(_DevView(self.ptr + self.z_offset, (self.height, self.width), "<f4"), device=f"cuda:{local_device}")
+            self.counter = torch.as_tensor(_DevView(self.ptr + self.counter_offset, (1,), "<i4"), device=f"cuda:{local_device}")
+
+    def render(self, dev_scene, opts):
+        """Enqueues this rank's part of one frame on the current stream (asynchronous)."""
+        stream = torch.cuda.current_stream().cuda_stream
+        if self.rank == 0:
+            self.counter.zero_()
+        dist.all_reduce(self.token, group=self.group)  # counter zeroed before anybody pulls
+        dev_scene.render_device_shared(opts, self.ptr, self.ptr + self.z_offset, stream, self.share)
+
+    def complete(self):
+        """After render(): the frame is complete on rank 0 once every rank's kernel has finished."""
+        dist.all_reduce(self.token, group=self.group)
+
+    def close(self):
+        from . import device as _device
+        if getattr(self, "ptr", None):
+            self.raster = self.z = self.counter = None
+            torch.cuda.synchronize()
+            dist.barrier(group=self.group)
+            _device.shared_release(self.local_device, self.ptr, self.rank == 0)
+            self.ptr = None

@@ -242,6 +242,54 @@ int crt_render_device(crt_scene *scene, const crt_render_opts *opts,
 	float *d_raster, float *d_z_buffer, void *cuda_stream);
 int crt_render_device_sync(crt_scene *scene, crt_stats *stats);
 
+/* ---- one frame rendered by several devices (or processes) -------------------------
+ * The reference parallelises inside render() itself (render.c:349-352: OpenMP threads over
+ * rows, thread count from -m, system.c:54-74).  Here several scenes -- replicas of the same
+ * description on different devices -- drain ONE work queue: every resident warp of every
+ * participant pulls the next work unit (8 pixels; 2 pixels for the last part of the frame)
+ * from `work_counter` with a system-scope atomic and writes its pixels straight into the
+ * common frame.  work_counter, d_raster and d_z_buffer must be visible to every
+ * participant: memory of one device mapped into the others by peer access
+ * (cudaDeviceEnablePeerAccess over NVLink) or CUDA IPC; the owner zeroes work_counter
+ * before the participants enqueue the frame.  Load balance is dynamic down to the last
+ * unit; the frame does not depend on which device renders which unit (counter-based RNG,
+ * fixed-order sums), so it is bit-identical to the single-device frame. */
+typedef struct crt_frame_share {
+	unsigned int *work_counter; /* one 32-bit counter, zero at the start of the frame */
+	uint32_t total_warps;       /* sum of crt_scene_resident_warps() over the participants */
+	uint32_t reserved[5];
+} crt_frame_share;
+
+/* resident warps of the render kernel on the scene's device (the persistent grid) */
+int crt_scene_resident_warps(crt_scene *scene, const crt_render_opts *opts, uint32_t *warps);
+/* crt_render_device() as one participant of a shared frame (share == NULL: alone) */
+int crt_render_device_shared(crt_scene *scene, const crt_render_opts *opts,
+	float *d_raster, float *d_z_buffer, void *cuda_stream, const crt_frame_share *share);
+
+/* Memory of one device made visible to other PROCESSES on the same node (one process per GPU,
+ * torchrun): the owner allocates and passes `handle` to the others (any byte transport), who map
+ * it with crt_shared_open() -- CUDA IPC, peer access over NVLink.  Used for the common frame and
+ * the work counter of crt_frame_share. */
+#define CRT_IPC_HANDLE_BYTES 64
+int crt_shared_alloc(int device, size_t bytes, void **d_ptr, unsigned char handle[CRT_IPC_HANDLE_BYTES]);
+int crt_shared_open(int device, const unsigned char handle[CRT_IPC_HANDLE_BYTES], void **d_ptr);
+int crt_shared_release(int device, void *d_ptr, int owner);
+
+/* The same within one process: the scene replicated on `num_devices` CUDA devices (the BVH is
+ * built once), frame and work counter on devices[0], the others reach them by peer access.
+ * Without peer access the devices render static shards (crt_render_opts.shard_*) that are
+ * merged on the host.  A device may be listed twice (two replicas on one GPU). */
+typedef struct crt_multi crt_multi;
+int crt_multi_create(const crt_scene_desc *desc, const int *devices, int num_devices, crt_multi **out);
+void crt_multi_destroy(crt_multi *multi);
+int crt_multi_num_devices(const crt_multi *multi);
+int crt_multi_is_dynamic(const crt_multi *multi); /* 1: shared queue over peer access, 0: static shards */
+int crt_multi_get_info(const crt_multi *multi, int index, crt_scene_info *info);
+/* replaces render(): HOST buffers as crt_render(); device_ms (may be NULL) receives the
+ * render-kernel time of every device */
+int crt_multi_render(crt_multi *multi, const crt_render_opts *opts,
+	float *raster, float *z_buffer, crt_stats *stats, double *device_ms);
+
 /* Ray-batch seams (tests, tools).  rays = n * 6 floats: direction xyz then
  * point xyz, the layout of `struct Ray` (object.h:27-30).
  * crt_trace_closest replaces get_closest_intersection() (render.c:118-124):

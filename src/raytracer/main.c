@@ -43,6 +43,8 @@ static const char *const HELP_TEXT =
 static const char *const HELP_EXTRA =
 	"B200 BUILD, ADDITIONAL PARAMETERS:\n"
 	"[--device] (integer)             : DEFAULT = 0       : CUDA device the trace loop runs on ([-m] is accepted and ignored).\n"
+	"[--gpus] (integer | \"max\")       : DEFAULT = 1       : number of CUDA devices that share the frame (devices 0 .. N-1).\n"
+	"[--devices] (list)               : DEFAULT = none    : comma-separated CUDA devices that share the frame, e.g. 0,2,3.\n"
 	"[--seed] (integer)               : DEFAULT = 1       : seed of the counter-based sampling stream.\n"
 	"[--stats]                        : DEFAULT = OFF     : count rays and intersection tests, print Mrays/s.\n";
 
@@ -85,11 +87,41 @@ int main(int argc, char *argv[])
 	const int d = rt_args_find_with_values(&args, "--device", 1);
 	const int device = d ? atoi(argv[d + 1]) : 0;
 
+	/* --gpus N / --devices a,b,c: several devices drain one work queue (crt_multi_render) */
+	int devices[64], num_devices = 0;
+	const int dl = rt_args_find_with_values(&args, "--devices", 1);
+	const int gn = rt_args_find_with_values(&args, "--gpus", 1);
+	if (dl) {
+		const char *c = argv[dl + 1];
+		while (*c && num_devices < 64) {
+			devices[num_devices++] = atoi(c);
+			while (*c && *c != ',')
+				c++;
+			if (*c == ',')
+				c++;
+		}
+	} else if (gn) {
+		int n = !strcmp(argv[gn + 1], "max") ? crt_device_count() : atoi(argv[gn + 1]);
+		if (n > 64)
+			n = 64;
+		for (int k = 0; k < n; k++)
+			devices[num_devices++] = k;
+	}
+
 	rt_log("Commencing raytracing.");
 	crt_stats stats;
 	crt_scene_info info;
-	if (rt_render(&scene, &image, &opts, device, &stats, &info, err))
+	if (num_devices > 1) {
+		double device_ms[64];
+		int dynamic = 0;
+		rt_log("Using %d CUDA devices.", num_devices);
+		if (rt_render_multi(&scene, &image, &opts, devices, num_devices, &stats, &info, device_ms, &dynamic, err))
+			rt_fatal("%s", err);
+		for (int k = 0; k < num_devices; k++)
+			rt_log("Device %d: trace kernel %.3f ms (%s).", devices[k], device_ms[k], dynamic ? "shared work queue" : "static shard");
+	} else if (rt_render(&scene, &image, &opts, num_devices == 1 ? devices[0] : device, &stats, &info, err)) {
 		rt_fatal("%s", err);
+	}
 	rt_log("BVH: %u nodes over %u primitives, depth %u, built in %.1f ms; trace kernel %.3f ms, call %.3f ms.",
 		info.num_nodes, info.num_bounded, info.max_depth, info.build_ms, stats.kernel_ms, stats.total_ms);
 	if (opts.flags & CRT_RENDER_COUNT_STATS) {

@@ -28,4 +28,10 @@ void rt_render_set_view(crt_render_opts *opts, const struct rt_scene *scene, con
 int rt_render(const struct rt_scene *scene, struct rt_image *img, const crt_render_opts *opts,
 	int device, crt_stats *stats, crt_scene_info *info, char *err);
 
+/* the same on several CUDA devices at once (the reference's -m: render.c:349-352 runs the rows on
+ * OpenMP threads): scene replicated, one dynamic work queue over all devices (crt_multi_render);
+ * device_ms: num_devices values or NULL; dynamic: 1 shared queue over peer access, 0 static shards */
+int rt_render_multi(const struct rt_scene *scene, struct rt_image *img, const crt_render_opts *opts,
+	const int *devices, int num_devices, crt_stats *stats, crt_scene_info *info, double *device_ms, int *dynamic, char *err);
+
 #endif
