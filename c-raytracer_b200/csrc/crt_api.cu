@@ -448,11 +448,12 @@ int crt_render_device_shared(crt_scene *s, const crt_render_opts *opts, float *d
 	if (opts->max_bounces > kMaxBounces)
 		return fail(CRT_ERR_INVALID, "max_bounces %u exceeds the supported %u", opts->max_bounces, kMaxBounces);
 	/* the per-frame scratch (work counter, pending stacks, contribution slots, events) belongs to
-	 * the scene: one frame in flight per crt_scene */
-	if (s->frame_pending)
-		return fail(CRT_ERR_INVALID, "a frame of this scene is still in flight: call crt_render_device_sync() first");
+	 * the scene: one frame in flight per crt_scene (see the stream wait below) */
 	CUDA_TRY(cudaSetDevice(s->device));
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	/* a frame enqueued earlier and not yet synchronised: this one starts after it, whatever the stream */
+	if (s->frame_pending)
+		CUDA_TRY(cudaStreamWaitEvent(stream, s->ev_stop, 0));
 	const size_t pixels = static_cast<size_t>(opts->width) * opts->height;
 	const bool count = (opts->flags & CRT_RENDER_COUNT_STATS) != 0;
 

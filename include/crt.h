@@ -236,8 +236,10 @@ int crt_render(crt_scene *scene, const crt_render_opts *opts,
  * default stream) without synchronising.  stats (may be NULL) is filled only
  * by crt_render_device_sync().  ONE frame in flight per crt_scene: the work
  * counter, pending-ray stacks and timing events are the scene's, so a second
- * crt_render_device() before crt_render_device_sync() fails with
- * CRT_ERR_INVALID (render several frames concurrently from several scenes). */
+ * crt_render_device() before crt_render_device_sync() is ordered AFTER the first
+ * (its stream waits for the first frame's end event, whatever stream that ran on)
+ * and the first frame's statistics are lost; render several frames concurrently
+ * from several scenes. */
 int crt_render_device(crt_scene *scene, const crt_render_opts *opts,
 	float *d_raster, float *d_z_buffer, void *cuda_stream);
 int crt_render_device_sync(crt_scene *scene, crt_stats *stats);

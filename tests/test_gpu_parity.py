@@ -436,3 +436,27 @@ def test_error_codes(gpu):
     assert L.crt_scene_create(C.addressof(sc.desc), 9999, C.byref(h)) == _abi.CRT_ERR_INVALID
     with pytest.raises(device.CrtError):
         dev.texture(-1, np.zeros((1, 3), np.float32))
+
+
+def test_frames_enqueued_without_sync_are_ordered(gpu):
+    """One frame in flight per scene (include/crt.h): a second crt_render_device() before the sync,
+    on ANOTHER stream and at another size, starts after the first one -- the per-scene work counter
+    and scratch are never shared by two running kernels."""
+    import torch
+    sc, dev = dev_scene("scene5_small")
+    o1 = sc.options(320, 180, "-g", "path", "-n", "2")
+    o2 = sc.options(200, 100)
+    want1, _ = dev.render(o1)
+    want2, want_z2 = dev.render(o2)
+    r1 = torch.empty((180, 320, 3), dtype=torch.float32, device="cuda:0")
+    z1 = torch.empty((180, 320), dtype=torch.float32, device="cuda:0")
+    r2 = torch.empty((100, 200, 3), dtype=torch.float32, device="cuda:0")
+    z2 = torch.empty((100, 200), dtype=torch.float32, device="cuda:0")
+    sa, sb = torch.cuda.Stream(device=0), torch.cuda.Stream(device=0)
+    dev.render_device(o1, r1.data_ptr(), z1.data_ptr(), sa.cuda_stream)
+    dev.render_device(o2, r2.data_ptr(), z2.data_ptr(), sb.cuda_stream)
+    dev.sync()
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(r1.cpu().numpy(), want1)
+    np.testing.assert_array_equal(r2.cpu().numpy(), want2)
+    np.testing.assert_array_equal(z2.cpu().numpy(), want_z2)
