@@ -66,6 +66,7 @@ IMAGE_CASES = [
 BENCH_CASES = [
     ("scene5_n16", "scene5", 480, 270, ("-g", "path", "-n", "16"), "meshes/dragon.stl"),
     ("scene6_n4", "scene6", 480, 270, ("-g", "path", "-n", "4"), "meshes/menger_sponge.stl"),
+    ("scene6_n64", "scene6", 240, 135, ("-g", "path", "-n", "64"), "meshes/menger_sponge.stl"),  # BASELINE configs[4] flags
 ]
 
 RAY_SCENES = ["scene1", "scene3", "scene4", "scenetest", "scenetest2", "scene5_small", "scene6_small"]
@@ -107,7 +108,10 @@ def main():
 
     if os.environ.get("GOLDEN_BENCH"):
         import hashlib
+        only = os.environ.get("GOLDEN_ONLY")
         for name, scene, w, h, flags, mesh in BENCH_CASES:
+            if only and name != only:
+                continue
             path = os.path.join("scenes", scene + ".json")
             raster, z, cnt = oracle.ref_render(path, w, h, flags, seed=1)
             other, _, _ = oracle.ref_render(path, w, h, flags, seed=2)

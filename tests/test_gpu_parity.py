@@ -355,10 +355,10 @@ def test_full_geometry_small_frame_vs_oracle(gpu, scene, flags):
     assert abs(int(st.rays_shadow) - int(ost.rays_shadow)) <= 1e-3 * ost.rays_shadow
 
 
-@pytest.mark.parametrize("name", ["scene5_n16", "scene6_n4"])
+@pytest.mark.parametrize("name", ["scene5_n16", "scene6_n4", "scene6_n64"])
 def test_bench_flags_match_reference_golden(gpu, name):
     """The benchmark workloads' own flags (bench.py: scene5 -g path -n 16; configs[4]: scene6 path
-    traced) on the benchmark geometry at 480x270, against frames the UNMODIFIED reference rendered
+    traced, -n 4 at 480x270 and the 4K run's -n 64 at 240x135) on the benchmark geometry, against frames the UNMODIFIED reference rendered
     (tests/golden/bench_*.npz, make_golden.py with GOLDEN_BENCH=1; 128 s of the reference for the
     dragon).  The mesh is generated (tools/gen_meshes.py): its SHA-256 is stored beside the frame."""
     import hashlib
