@@ -7,7 +7,7 @@ import ctypes as C
 
 import numpy as np
 
-CRT_ABI_VERSION = 1
+CRT_ABI_VERSION = 2
 
 CRT_OBJ_SPHERE, CRT_OBJ_TRIANGLE, CRT_OBJ_PLANE = 0, 1, 2
 CRT_TEX_UNIFORM, CRT_TEX_CHECKERBOARD, CRT_TEX_BRICK, CRT_TEX_NOISY_PERIODIC = 0, 1, 2, 3
@@ -70,6 +70,7 @@ class Stats(C.Structure):
         ("nodes_shaded", C.c_uint64), ("kernel_ms", C.c_double), ("total_ms", C.c_double),
         ("node_steps", C.c_uint64), ("node_step_lanes", C.c_uint64), ("node_step_idle", C.c_uint64),
         ("prim_steps", C.c_uint64), ("prim_step_lanes", C.c_uint64), ("prim_step_idle", C.c_uint64),
+        ("queue_ms", C.c_double), ("last_warp_ms", C.c_double), ("warp_busy_ms", C.c_double),
     ]
 
     def as_dict(self):
@@ -81,6 +82,7 @@ class Stats(C.Structure):
             "total_ms": float(self.total_ms),
             "node_steps": int(self.node_steps), "node_step_lanes": int(self.node_step_lanes), "node_step_idle": int(self.node_step_idle),
             "prim_steps": int(self.prim_steps), "prim_step_lanes": int(self.prim_step_lanes), "prim_step_idle": int(self.prim_step_idle),
+            "queue_ms": float(self.queue_ms), "last_warp_ms": float(self.last_warp_ms), "warp_busy_ms": float(self.warp_busy_ms),
         }
 
 

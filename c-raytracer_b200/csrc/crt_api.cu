@@ -88,6 +88,7 @@ struct crt_scene {
 	cudaStream_t last_stream = nullptr;
 	bool frame_pending = false;
 	bool frame_counted = false;
+	uint32_t frame_warps = 0;
 	size_t wide_bytes = 0;   /* size of d.wide: the window of the optional L2 persistence (CRT_L2_PERSIST_MB) */
 	size_t persist_bytes = 0;
 };
@@ -358,7 +359,7 @@ static int upload_host_scene(const HostScene &h, int device, crt_scene **out)
 	if (!rc) rc = upload(s, h.mats, &s->d.materials);
 	if (!rc && cudaMalloc(&s->tile_counter, sizeof(unsigned int)) != cudaSuccess)
 		rc = fail(CRT_ERR_CUDA, "cudaMalloc(tile counter) failed");
-	if (!rc && cudaMalloc(&s->counters, kNumCounters * sizeof(unsigned long long)) != cudaSuccess)
+	if (!rc && cudaMalloc(&s->counters, kTotalCounters * sizeof(unsigned long long)) != cudaSuccess)
 		rc = fail(CRT_ERR_CUDA, "cudaMalloc(counters) failed");
 	if (!rc && (cudaEventCreate(&s->ev_start) != cudaSuccess || cudaEventCreate(&s->ev_stop) != cudaSuccess))
 		rc = fail(CRT_ERR_CUDA, "cudaEventCreate failed");
@@ -560,7 +561,7 @@ int crt_render_device_shared(crt_scene *s, const crt_render_opts *opts, float *d
 
 	if (!share)
 		CUDA_TRY(cudaMemsetAsync(s->tile_counter, 0, sizeof(unsigned int), stream));
-	CUDA_TRY(cudaMemsetAsync(s->counters, 0, kNumCounters * sizeof(unsigned long long), stream));
+	CUDA_TRY(cudaMemsetAsync(s->counters, 0, kTotalCounters * sizeof(unsigned long long), stream));
 	/* pixels of other shards (and misses) are zero: the reference relies on fresh zero pages */
 	if (!share) { /* the participants of a shared frame write every pixel between them */
 		CUDA_TRY(cudaMemsetAsync(d_raster, 0, 3 * pixels * sizeof(float), stream));
@@ -574,6 +575,7 @@ int crt_render_device_shared(crt_scene *s, const crt_render_opts *opts, float *d
 	s->last_stream = stream;
 	s->frame_pending = true;
 	s->frame_counted = count;
+	s->frame_warps = static_cast<uint32_t>(grid) * kWarpsPerBlock;
 	return CRT_OK;
 }
 
@@ -592,7 +594,7 @@ int crt_render_device_sync(crt_scene *s, crt_stats *stats)
 		CUDA_TRY(cudaEventElapsedTime(&ms, s->ev_start, s->ev_stop));
 		stats->kernel_ms = ms;
 		if (s->frame_counted) {
-			unsigned long long c[kNumCounters];
+			unsigned long long c[kTotalCounters];
 			CUDA_TRY(cudaMemcpy(c, s->counters, sizeof c, cudaMemcpyDeviceToHost));
 			stats->rays_closest = c[0];
 			stats->rays_shadow = c[1];
@@ -611,6 +613,12 @@ int crt_render_device_sync(crt_scene *s, crt_stats *stats)
 			stats->prim_steps = c[14];
 			stats->prim_step_lanes = c[15];
 			stats->prim_step_idle = c[16];
+			if (c[kTimeStart]) {
+				const unsigned long long first = ~c[kTimeStart], dry = ~c[kTimeDry];
+				stats->queue_ms = static_cast<double>(dry - first) * 1e-6;
+				stats->last_warp_ms = static_cast<double>(c[kTimeEnd] - first) * 1e-6;
+				stats->warp_busy_ms = static_cast<double>(c[kTimeBusy]) * 1e-6 / (s->frame_warps ? s->frame_warps : 1u);
+			}
 		}
 	}
 	return CRT_OK;
@@ -774,6 +782,9 @@ static void add_stats(crt_stats &acc, const crt_stats &st)
 	acc.prim_steps += st.prim_steps;
 	acc.prim_step_lanes += st.prim_step_lanes;
 	acc.prim_step_idle += st.prim_step_idle;
+	acc.queue_ms = std::max(acc.queue_ms, st.queue_ms);
+	acc.last_warp_ms = std::max(acc.last_warp_ms, st.last_warp_ms);
+	acc.warp_busy_ms = std::max(acc.warp_busy_ms, st.warp_busy_ms);
 	acc.kernel_ms = std::fmax(acc.kernel_ms, st.kernel_ms);
 }
 
@@ -953,6 +964,29 @@ int crt_shared_release(int device, void *d_ptr, int owner)
 		CUDA_TRY(cudaFree(d_ptr));
 	else
 		CUDA_TRY(cudaIpcCloseMemHandle(d_ptr));
+	return CRT_OK;
+}
+
+/* ---- the caller's frame buffers, page-locked ------------------------------------ */
+
+int crt_host_register(void *ptr, size_t bytes)
+{
+	if (!ptr || !bytes)
+		return fail(CRT_ERR_INVALID, "NULL or empty host range");
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) {
+		cudaGetLastError();
+		return fail(CRT_ERR_NO_DEVICE, "no CUDA device available (this library has no CPU fallback)");
+	}
+	CUDA_TRY(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+	return CRT_OK;
+}
+
+int crt_host_unregister(void *ptr)
+{
+	if (!ptr)
+		return CRT_OK;
+	CUDA_TRY(cudaHostUnregister(ptr));
 	return CRT_OK;
 }
 

@@ -162,6 +162,13 @@ __device__ __forceinline__ void flush_counters(const RenderParams &p, Counters &
 	}
 }
 
+__device__ __forceinline__ unsigned long long device_clock_ns()
+{
+	unsigned long long t;
+	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+	return t;
+}
+
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(const RenderParams p)
 {
@@ -178,6 +185,7 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 	/* the lane's traversal stacks (closest-hit walk, then the shadow walks): shared memory, [slot][lane] */
 	const SharedStacks stacks(wstacks + warp_local * (kLaneStackWords * 32) + lane,
 		p.deep ? p.deep + (size_t)warp_global * p.deep_depth * 32 + lane : nullptr);
+	const unsigned long long warp_t0 = COUNT ? device_clock_ns() : 0ull;
 
 	for (;;) {
 		/* ---- next tile of this shard ------------------------------------- */
@@ -190,8 +198,16 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 		if (lane == 0)
 			unit = p.system_counter ? atomicAdd_system(p.tile_counter, 1u) : atomicAdd(p.tile_counter, 1u);
 		unit = __shfl_sync(kFull, unit, 0);
-		if (unit >= p.num_units)
+		if (unit >= p.num_units) {
+			if (COUNT && lane == 0) { /* crt_stats.queue_ms / warp_busy_ms / last_warp_ms */
+				const unsigned long long t = device_clock_ns();
+				atomicMax(p.counters + kTimeStart, ~warp_t0);
+				atomicMax(p.counters + kTimeDry, ~t);
+				atomicMax(p.counters + kTimeEnd, t);
+				atomicAdd(p.counters + kTimeBusy, t - warp_t0);
+			}
 			break;
+		}
 		uint32_t local_tile = unit, pix_lane = lane;
 		bool lane_on = true;
 		if (unit >= p.micro_from) {

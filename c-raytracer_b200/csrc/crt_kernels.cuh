@@ -31,6 +31,10 @@ constexpr int kBlockThreads = kWarpsPerBlock * 32;
 constexpr int kInnerPerVote = CRT_INNER_PER_VOTE, kPrimPerVote = CRT_PRIM_PER_VOTE; /* unit steps per warp vote */
 constexpr int kInnerWeight = CRT_INNER_WEIGHT, kPrimWeight = CRT_PRIM_WEIGHT;       /* node step iff ready_inner * Wi >= ready_prim * Wp */
 constexpr int kNumCounters = 17;
+/* instrumented instance: device clock (globaltimer, ns) marks after the event counters --
+ * ~min warp start, max warp end, sum of warp lifetimes, ~min time a warp found the queue empty */
+constexpr int kTimeStart = kNumCounters, kTimeEnd = kNumCounters + 1, kTimeBusy = kNumCounters + 2, kTimeDry = kNumCounters + 3;
+constexpr int kTotalCounters = kNumCounters + 4;
 #ifndef CRT_MICRO_PIXELS
 #define CRT_MICRO_PIXELS 2                 /* pixels per work unit in the final phase of a frame */
 #endif
@@ -61,7 +65,7 @@ struct RenderParams {
 	uint32_t num_units;             /* fine_from tiles + rows of the next tiles + micro units of the last tiles */
 	unsigned int *tile_counter;
 	uint32_t system_counter;        /* the counter is shared with other devices (peer / IPC mapping): system-scope atomics */
-	unsigned long long *counters;   /* kNumCounters, instrumented instance only */
+	unsigned long long *counters;   /* kTotalCounters, instrumented instance only */
 	float *pending;                 /* per-lane pending-ray stacks */
 	float *slots;                   /* per-warp shadow-ray contribution slots: 3 * kSlots floats each */
 	uint32_t pending_depth;

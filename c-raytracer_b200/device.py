@@ -19,7 +19,7 @@ SYMBOLS = [
     "crt_scene_create", "crt_scene_destroy", "crt_scene_get_info",
     "crt_render", "crt_render_device", "crt_render_device_sync",
     "crt_scene_resident_warps", "crt_render_device_shared",
-    "crt_shared_alloc", "crt_shared_open", "crt_shared_release",
+    "crt_shared_alloc", "crt_shared_open", "crt_shared_release", "crt_host_register", "crt_host_unregister",
     "crt_multi_create", "crt_multi_destroy", "crt_multi_num_devices", "crt_multi_is_dynamic", "crt_multi_get_info", "crt_multi_render",
     "crt_trace_closest", "crt_trace_shadow", "crt_texture_eval", "crt_measure_fp32_peak",
     "crt_postprocess", "crt_postprocess_device",
@@ -52,6 +52,8 @@ def lib():
         L.crt_shared_alloc.argtypes = [C.c_int, C.c_size_t, C.POINTER(C.c_void_p), C.c_void_p]
         L.crt_shared_open.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
         L.crt_shared_release.argtypes = [C.c_int, C.c_void_p, C.c_int]
+        L.crt_host_register.argtypes = [C.c_void_p, C.c_size_t]
+        L.crt_host_unregister.argtypes = [C.c_void_p]
         L.crt_multi_create.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
         L.crt_multi_destroy.argtypes = [C.c_void_p]
         L.crt_multi_destroy.restype = None
@@ -197,6 +199,15 @@ def shared_open(dev, handle):
     h = (C.c_ubyte * 64).from_buffer_copy(handle)
     _check(lib().crt_shared_open(dev, h, C.byref(p)))
     return p.value
+
+
+def host_register(array):
+    """crt_host_register on a numpy array the caller keeps alive; undo with host_unregister()."""
+    _check(lib().crt_host_register(C.c_void_p(array.ctypes.data), array.nbytes))
+
+
+def host_unregister(array):
+    _check(lib().crt_host_unregister(C.c_void_p(array.ctypes.data)))
 
 
 def shared_release(dev, ptr, owner):

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define CRT_ABI_VERSION 1
+#define CRT_ABI_VERSION 2
 
 enum crt_status {
 	CRT_OK = 0,
@@ -195,6 +195,10 @@ typedef struct crt_stats {
 	 * refill); 32 * steps - lanes - idle = lanes whose ray only had work of the other kind */
 	uint64_t node_steps, node_step_lanes, node_step_idle;
 	uint64_t prim_steps, prim_step_lanes, prim_step_idle;
+	/* the persistent grid's time line (instrumented instance, device clock): from the first warp's start
+	 * until a warp first found the work queue empty, until the last warp ended, and the mean life of a warp --
+	 * last_warp_ms - queue_ms is the tail, last_warp_ms - warp_busy_ms the mean idle time of a warp slot */
+	double queue_ms, last_warp_ms, warp_busy_ms;
 } crt_stats;
 
 typedef struct crt_scene crt_scene; /* opaque; owns all device memory */
@@ -267,6 +271,14 @@ int crt_scene_resident_warps(crt_scene *scene, const crt_render_opts *opts, uint
 /* crt_render_device() as one participant of a shared frame (share == NULL: alone) */
 int crt_render_device_shared(crt_scene *scene, const crt_render_opts *opts,
 	float *d_raster, float *d_z_buffer, void *cuda_stream, const crt_frame_share *share);
+
+/* Page-locks a host range the caller owns (the reference's image.raster / image.z_buffer,
+ * image.c:70-77, stay malloc'd): crt_render()'s device-to-host copies into a registered range run
+ * at the link's rate instead of through the driver's bounce buffer.  Worth it when the same
+ * buffers receive several frames (registering costs about as much as one pageable copy:
+ * BASELINE.md section 6).  Unregister before free(). */
+int crt_host_register(void *ptr, size_t bytes);
+int crt_host_unregister(void *ptr);
 
 /* Memory of one device made visible to other PROCESSES on the same node (one process per GPU,
  * torchrun): the owner allocates and passes `handle` to the others (any byte transport), who map

@@ -144,7 +144,7 @@ def read_dump(path):
     o += w * h * 4
     cnt = np.frombuffer(b[o:o + 32], dtype=np.uint64)
     secs = float(np.frombuffer(b[o + 32:o + 40], dtype=np.float64)[0])
-    return raster, z, {"cast_ray": int(cnt[0]), "closest_full": int(cnt[1]), "shadow": int(cnt[2]), "seconds": secs}
+    return raster, z, {"cast_ray": int(cnt[0]), "closest_full": int(cnt[1]), "shadow": int(cnt[2]), "box_tests": int(cnt[3]), "seconds": secs}
 
 
 def ref_render(scene_path, width, height, flags=(), seed=1, threads="max"):

@@ -158,6 +158,7 @@ static int mode_render(int argc, char **argv)
 	accel_init();
 	render_init();
 	ref_shim_bind((void *)cast_ray, (void *)get_closest_intersection, (void *)is_light_blocked);
+	ref_shim_bind_box((void *)bounding_cuboid_intersects);
 	memset(image.raster, 0, image.pixels * sizeof(v3)); /* reference relies on zero pages */
 	memset(image.z_buffer, 0, image.pixels * sizeof(float));
 
@@ -166,7 +167,7 @@ static int mode_render(int argc, char **argv)
 	if (idx)
 		max_b = (uint32_t)abs(atoi(myargv[idx + 1]));
 
-	uint64_t n_cast = 0, n_closest = 0, n_shadow = 0;
+	uint64_t n_cast = 0, n_closest = 0, n_shadow = 0, n_box = 0;
 	double t0 = system_time();
 	if (stock_loop) {
 		render(); /* reference loop, thread-local xorshift stream */
@@ -174,7 +175,7 @@ static int mode_render(int argc, char **argv)
 		const v3 kr = { 1.f, 1.f, 1.f };
 		/* same arithmetic as reference render.c:352-366, incl. the running
 		 * sum along the row */
-#pragma omp parallel for schedule(dynamic, 1) reduction(+ : n_cast, n_closest, n_shadow)
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : n_cast, n_closest, n_shadow, n_box)
 		for (uint32_t row = 0; row < image.resolution[Y]; row++) {
 			v3 pixel_position;
 			mul3s(image.vectors[Y], row, pixel_position);
@@ -197,6 +198,7 @@ static int mode_render(int argc, char **argv)
 			n_cast += c.cast_ray;
 			n_closest += c.closest_full;
 			n_shadow += c.shadow;
+			n_box += c.box_tests;
 		}
 	}
 	double t1 = system_time();
@@ -208,13 +210,13 @@ static int mode_render(int argc, char **argv)
 	fwrite(hdr, sizeof hdr, 1, f);
 	fwrite(image.raster, sizeof(v3), image.pixels, f);
 	fwrite(image.z_buffer, sizeof(float), image.pixels, f);
-	uint64_t cnt[4] = { n_cast, n_closest, n_shadow, 0 };
+	uint64_t cnt[4] = { n_cast, n_closest, n_shadow, n_box };
 	fwrite(cnt, sizeof cnt, 1, f);
 	double tm[2] = { t1 - t0, 0 };
 	fwrite(tm, sizeof tm, 1, f);
 	fclose(f);
-	printf("ref_engine: render %.3f s, cast_ray %llu, shadow %llu\n", t1 - t0,
-		(unsigned long long)n_cast, (unsigned long long)n_shadow);
+	printf("ref_engine: render %.3f s, cast_ray %llu, shadow %llu, box tests %llu\n", t1 - t0,
+		(unsigned long long)n_cast, (unsigned long long)n_shadow, (unsigned long long)n_box);
 	return 0;
 }
 

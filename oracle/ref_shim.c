@@ -55,7 +55,7 @@ static _Thread_local uint32_t tl_xs = 0;
 static _Thread_local struct ref_counters tl_cnt;
 
 /* addresses of the instrumented functions, filled by ref_shim_bind() */
-static void *fn_cast_ray, *fn_closest, *fn_blocked;
+static void *fn_cast_ray, *fn_closest, *fn_blocked, *fn_box;
 
 static struct timespec start_t;
 
@@ -64,6 +64,11 @@ void ref_shim_bind(void *cast_ray_fn, void *closest_fn, void *blocked_fn)
 	fn_cast_ray = cast_ray_fn;
 	fn_closest = closest_fn;
 	fn_blocked = blocked_fn;
+}
+
+void ref_shim_bind_box(void *box_fn)
+{
+	fn_box = box_fn;
 }
 
 void ref_shim_begin_pixel(uint32_t seed, uint32_t pixel)
@@ -102,7 +107,9 @@ void ref_shim_reset_counters(void)
 __attribute__((no_instrument_function)) void __cyg_profile_func_enter(void *fn, void *site)
 {
 	(void)site;
-	if (fn == fn_cast_ray) {
+	if (fn == fn_box) { /* by far the most frequent instrumented call */
+		tl_cnt.box_tests++;
+	} else if (fn == fn_cast_ray) {
 		tl_cnt.cast_ray++;
 		if (!tl_active)
 			return;

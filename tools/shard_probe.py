@@ -34,6 +34,16 @@ def main():
     whole = timed(o)
     parts = [timed(multigpu.shard_options(sc.options(w, h, *flags), k, n)) for k in range(n)]
     print(f"{scene} {w}x{h} {' '.join(flags)}: whole frame {whole:.2f} ms; whole/{n} = {whole / n:.2f} ms")
+
+    def timeline(opts, label):
+        opts.flags |= abi.CRT_RENDER_COUNT_STATS
+        st = abi.Stats()
+        dev.render(opts, st)
+        print(f"  {label} (instrumented): kernel {st.kernel_ms:.2f} ms; queue dry after {st.queue_ms:.2f} ms, last warp ends at "
+              f"{st.last_warp_ms:.2f} ms (tail {st.last_warp_ms - st.queue_ms:.2f} ms), mean warp life {st.warp_busy_ms:.2f} ms")
+
+    timeline(sc.options(w, h, *flags), "whole frame")
+    timeline(multigpu.shard_options(sc.options(w, h, *flags), 0, n), f"shard 0 of {n}")
     print(f"  shards alone: {' '.join(f'{p:.2f}' for p in parts)} ms; sum {sum(parts):.2f} ms ({sum(parts) / whole:.3f} x), max {max(parts):.2f} ms")
 
 
