@@ -510,29 +510,49 @@ int crt_render_device_shared(crt_scene *s, const crt_render_opts *opts, float *d
 	p.refill = kRefill;
 	if (const char *e = std::getenv("CRT_REFILL"))
 		p.refill = static_cast<uint32_t>(std::min(32, std::max(1, std::atoi(e))));
-	/* tiles from fine_from on are handed out as quarter tiles (one 8-pixel row per warp): bounds
-	 * the tail of the persistent grid and keeps a warp's shading points close together */
+	/* work units (crt_kernels.cu): a few neighbouring pixels each -- bounds the tail of the persistent
+	 * grid and keeps a warp's shading points close together (whole 8x4 tiles were never faster) */
 	{
 		/* a shared frame is drained by the resident warps of every participant */
 		const uint32_t warps = share ? share->total_warps : static_cast<uint32_t>(grid) * kWarpsPerBlock;
-		uint32_t fine = p.num_local_tiles; /* measured: quarter tiles throughout are never slower (profiles/) */
-		if (const char *e = std::getenv("CRT_FINE_PERCENT"))
-			fine = static_cast<uint32_t>(static_cast<uint64_t>(p.num_local_tiles) * std::min(100, std::max(0, std::atoi(e))) / 100u);
-		p.fine_from = p.num_local_tiles - fine;
-		/* the last tiles a few pixels at a time: CRT_MICRO_PER_WARP pixels per resident warp */
-		uint32_t micro_pixels = CRT_MICRO_PIXELS, per_warp = CRT_MICRO_PER_WARP;
-		if (const char *e = std::getenv("CRT_MICRO_PIXELS"))
-			micro_pixels = static_cast<uint32_t>(std::atoi(e));
-		if (const char *e = std::getenv("CRT_MICRO_PER_WARP"))
-			per_warp = static_cast<uint32_t>(std::max(0, std::atoi(e)));
-		if (micro_pixels != 1u && micro_pixels != 2u && micro_pixels != 4u)
-			micro_pixels = CRT_MICRO_PIXELS;
+		/* lanes per pixel: part of the frame's arithmetic (the order its GI samples are summed in),
+		 * so it depends on the options alone -- never on the device count or the unit shape */
+		uint32_t gi_lanes = CRT_GI_LANES;
+		if (const char *e = std::getenv("CRT_GI_LANES"))
+			gi_lanes = static_cast<uint32_t>(std::atoi(e));
+		if (gi_lanes != 1u && gi_lanes != 2u && gi_lanes != 4u && gi_lanes != 8u && gi_lanes != 16u && gi_lanes != 32u)
+			gi_lanes = CRT_GI_LANES;
+		const bool split = opts->gi_model == CRT_GI_PATH && opts->samples_per_pixel > 1u && opts->max_bounces > 0u;
+		p.gshift = 0;
+		if (split)
+			while ((1u << p.gshift) < gi_lanes)
+				p.gshift++;
 		const uint32_t tile_pixels = kTileW * kTileH;
-		const uint32_t micro_tiles = static_cast<uint32_t>(std::min<uint64_t>(fine, (static_cast<uint64_t>(warps) * per_warp + tile_pixels - 1) / tile_pixels));
-		p.micro_pixels = micro_pixels;
-		p.micro_tile = p.num_local_tiles - micro_tiles;
-		p.micro_from = p.fine_from + (fine - micro_tiles) * kTileH;
-		p.num_units = p.micro_from + micro_tiles * (tile_pixels / micro_pixels);
+		p.fine_pixels = std::min<uint32_t>(kTileW, tile_pixels >> p.gshift);
+		/* units of s pixels while more than s * taper pixels per resident warp remain: a unit costs up to
+		 * ~16 times the mean of its pixels, and whatever starts late must be small (crt_kernels.cu) */
+		uint32_t taper = CRT_TAPER_PIXELS;
+		if (const char *e = std::getenv("CRT_TAPER_PIXELS"))
+			taper = static_cast<uint32_t>(std::max(0, std::atoi(e)));
+		const uint32_t T = p.num_local_tiles;
+		uint32_t first_tile = 0, first_unit = 0;
+		for (int i = 0; i < kPhases; i++) {
+			const uint32_t size = p.fine_pixels >> i;
+			if (!size) {
+				p.phase_unit[i] = 0xffffffffu;
+				p.phase_tile[i] = T;
+				continue;
+			}
+			p.phase_unit[i] = first_unit;
+			p.phase_tile[i] = first_tile;
+			/* tiles left when this phase ends */
+			uint64_t left = size > 1u ? (static_cast<uint64_t>(size) * taper * warps + tile_pixels - 1) / tile_pixels : 0u;
+			left = std::min<uint64_t>(left, T - first_tile);
+			const uint32_t end_tile = T - static_cast<uint32_t>(left);
+			first_unit += (end_tile - first_tile) * (tile_pixels / size);
+			first_tile = end_tile;
+		}
+		p.num_units = first_unit;
 	}
 	p.tile_counter = share ? share->work_counter : s->tile_counter;
 	p.system_counter = share ? 1u : 0u;

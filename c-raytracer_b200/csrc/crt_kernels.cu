@@ -188,12 +188,17 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 	const unsigned long long warp_t0 = COUNT ? device_clock_ns() : 0ull;
 
 	for (;;) {
-		/* ---- next tile of this shard ------------------------------------- */
-		/* work unit: a whole 8x4 tile, one 8-pixel row of a tile (lanes 0..7), or --
-		 * for the last tiles of the queue -- one or two pixels: an 8-pixel row through
-		 * the glass mesh is 20 to 100 ms of one warp, which would otherwise be the
-		 * tail of the persistent grid (and 1/8 of a frame has only 14 rows per warp).
-		 * A pixel's value does not depend on the shape of the unit it is traced in. */
+		/* ---- next unit of this shard -------------------------------------- */
+		/* work unit: p.fine_pixels neighbouring pixels of an 8x4 tile, then -- towards the end of
+		 * the queue -- 4, 2 and 1 of them: eight pixels through the glass mesh are 20 to 100 ms of
+		 * one warp, 16 times the mean, and a unit that starts late outlives everything handed
+		 * out after it (1/8 of a 4K frame measured a 22 ms tail on 104 ms with 8-pixel units up
+		 * to the last 64 pixels per warp; crt_api.cu sizes the phases).
+		 * A pixel is traced by 1 << p.gshift neighbouring lanes: with path-traced GI the lanes
+		 * of a pixel share its GI samples (sample k goes to lane k mod G; lane 0 of the pixel
+		 * also owns the direct light and the specular chain), their partial sums are added in
+		 * lane order at the end.  G is a property of the frame, not of the unit, so a pixel's
+		 * value does not depend on the unit it is traced in or on the devices that took part. */
 		uint32_t unit = 0;
 		if (lane == 0)
 			unit = p.system_counter ? atomicAdd_system(p.tile_counter, 1u) : atomicAdd(p.tile_counter, 1u);
@@ -208,19 +213,18 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 			}
 			break;
 		}
-		uint32_t local_tile = unit, pix_lane = lane;
-		bool lane_on = true;
-		if (unit >= p.micro_from) {
-			const uint32_t v = unit - p.micro_from, per_tile = (uint32_t)(kTileW * kTileH) / p.micro_pixels;
-			local_tile = p.micro_tile + v / per_tile;
-			pix_lane = (v % per_tile) * p.micro_pixels + lane;
-			lane_on = lane < p.micro_pixels;
-		} else if (unit >= p.fine_from) {
-			const uint32_t v = unit - p.fine_from;
-			local_tile = p.fine_from + v / (uint32_t)kTileH;
-			pix_lane = (v % (uint32_t)kTileH) * (uint32_t)kTileW + lane;
-			lane_on = lane < (uint32_t)kTileW;
-		}
+		/* lane's place among the lanes of its pixel: recomputed where it is needed, not kept in a register */
+		const auto lane_group = [&]() { return lane & ((1u << p.gshift) - 1u); };
+		/* which phase of the queue: units shrink from fine_pixels to one pixel towards its end */
+		uint32_t ph = 0;
+#pragma unroll
+		for (uint32_t i = 1; i < (uint32_t)kPhases; i++)
+			ph += unit >= p.phase_unit[i] ? 1u : 0u;
+		const uint32_t upx = p.fine_pixels >> ph, per_tile = (uint32_t)(kTileW * kTileH) / upx;
+		const uint32_t v = unit - p.phase_unit[ph];
+		const uint32_t local_tile = p.phase_tile[ph] + v / per_tile;
+		const uint32_t pix_lane = (v % per_tile) * upx + (lane >> p.gshift);
+		const bool lane_on = (lane >> p.gshift) < upx;
 		const uint32_t chunk = (local_tile / kChunkTiles) * o.shard_count + o.shard_index;
 		const uint32_t tile = chunk * kChunkTiles + local_tile % kChunkTiles;
 		const uint32_t tx = tile % p.tiles_x, ty = tile / p.tiles_x;
@@ -265,8 +269,10 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 					float dx, dy, dz;
 					gi_direction(r.dx, r.dy, r.dz, (r.aux >> 31) != 0u, crt_rand(r.node, draw), crt_rand(r.node, draw + 1u), dx, dy, dz);
 					const float w = (1.f / (float)n) * dot3(r.dx, r.dy, r.dz, dx, dy, dz);
-					if (k + 1u < n)
-						slot[9 * 32] = __uint_as_float(REC_GI | (k + 1u));
+					/* the lanes of a pixel take the samples of the primary hit in turn (deeper generators have n = 1) */
+					const uint32_t kn = k + (1u << p.gshift);
+					if (kn < n)
+						slot[9 * 32] = __uint_as_float(REC_GI | kn);
 					else
 						sp--;
 					r.dx = dx; r.dy = dy; r.dz = dz;
@@ -287,7 +293,10 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 			hit.object = -1;
 			hit.t = 0.f;
 			hit.slot = 0;
-			if (have) {
+			/* a pixel's other lanes take the primary hit from its first lane */
+			{
+			const bool ghost = primary && lane_group() != 0u;
+			if (have && !ghost) {
 				Cnt<COUNT>::add(cn.closest);
 				/* a NaN direction (total internal reflection) hits nothing */
 				if (ray.dx == ray.dx && ray.dy == ray.dy && ray.dz == ray.dz) {
@@ -297,6 +306,13 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 					if (!found)
 						hit = trace_closest<COUNT>(sc, ray, stacks, cn);
 				}
+			}
+			}
+			if (primary && p.gshift) { /* warp-uniform */
+				const uint32_t lead = lane - lane_group();
+				hit.t = __shfl_sync(kFull, hit.t, lead);
+				hit.object = __shfl_sync(kFull, hit.object, lead);
+				hit.slot = __shfl_sync(kFull, hit.slot, lead);
 			}
 			const bool is_hit = have && hit.object >= 0;
 
@@ -308,7 +324,9 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 			bool outside = false, lit = false;
 			int skip = -1;
 			if (is_hit) {
-				Cnt<COUNT>::add(cn.shaded);
+				const bool ghost = primary && lane_group() != 0u;
+				if (!ghost)
+					Cnt<COUNT>::add(cn.shaded);
 				hit_normal(sc, hit, ray, nx, ny, nz, mat_index, eps);
 				hx = __fadd_rn(__fmul_rn(ray.dx, hit.t), ray.ox);
 				hy = __fadd_rn(__fmul_rn(ray.dy, hit.t), ray.oy);
@@ -325,8 +343,10 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 					cg += __ldg(&m->ka[1]) * sc.ambient[1];
 					cb += __ldg(&m->ka[2]) * sc.ambient[2];
 				}
-				acc_r += cr * wr; acc_g += cg * wg; acc_b += cb * wb;
-				if (primary && o.max_bounces > 0u)
+				if (!ghost) {
+					acc_r += cr * wr; acc_g += cg * wg; acc_b += cb * wb;
+				}
+				if (primary && !ghost && o.max_bounces > 0u)
 					z_value = hit.t; /* render.c:304-305, :342 */
 				/* is the hit object itself an emitter? it is skipped as a light (render.c:172) */
 				uint32_t lights = sc.total_lights;
@@ -335,7 +355,7 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 						skip = (int)e;
 						lights -= sc.emitters[e].num_lights;
 					}
-				lit = outside && lights > 0u;
+				lit = outside && lights > 0u && !ghost;
 				if (lit) {
 					float tr, tg, tb;
 					texture_color(m, hx, hy, hz, tr, tg, tb);
@@ -558,6 +578,7 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 					acc_b += sum_b * wb;
 				}
 				if (r.remaining > 0u) {
+					const bool ghost = primary && lane_group() != 0u;
 					const crt_material *m = sc.materials + mat_index;
 					const uint32_t flags = __ldg(&m->flags);
 					uint32_t n_gi = 0;
@@ -566,7 +587,7 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 					uint32_t ordinal = n_gi;
 					bool spawn_r = false, spawn_t = false;
 					Pending rr, rt;
-					if (r.inside != hit.object && (flags & CRT_MAT_REFLECTIVE)) {
+					if (!ghost && r.inside != hit.object && (flags & CRT_MAT_REFLECTIVE)) {
 						/* render.c:308-317 */
 						rr.kr = r.kr * __ldg(&m->kr[0]); rr.kg = r.kg * __ldg(&m->kr[1]); rr.kb = r.kb * __ldg(&m->kr[2]);
 						if (o.min_intensity_sqr < xdot(rr.kr, rr.kg, rr.kb, rr.kr, rr.kg, rr.kb)) {
@@ -580,7 +601,7 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 							rr.aux = 0;
 						}
 					}
-					if (flags & CRT_MAT_TRANSPARENT) {
+					if (!ghost && (flags & CRT_MAT_TRANSPARENT)) {
 						/* refraction by explicit angles (render.c:320-340) */
 						rt.kr = r.kr * __ldg(&m->kt[0]); rt.kg = r.kg * __ldg(&m->kt[1]); rt.kb = r.kb * __ldg(&m->kt[2]);
 						if (o.min_intensity_sqr < xdot(rt.kr, rt.kg, rt.kb, rt.kr, rt.kg, rt.kb)) {
@@ -615,12 +636,14 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 						pending_store(pending_slot(p, warp_global, sp++, lane), rt);
 					if (spawn_r)
 						pending_store(pending_slot(p, warp_global, sp++, lane), rr);
-					if (n_gi > 0u) {
+					/* first GI sample of this lane: the primary hit's samples are dealt over the pixel's lanes */
+					const uint32_t k0 = primary ? lane_group() : 0u;
+					if (n_gi > k0) {
 						Pending g;
 						g.ox = hx; g.oy = hy; g.oz = hz;
 						g.dx = nx; g.dy = ny; g.dz = nz;
 						g.kr = wr; g.kg = wg; g.kb = wb;
-						g.remaining = REC_GI;
+						g.remaining = REC_GI | k0;
 						g.inside = (int32_t)n_gi;
 						g.node = r.node;
 						uint32_t lights = sc.total_lights;
@@ -635,7 +658,17 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 			primary = false;
 		}
 
-		if (in_image) {
+		/* a pixel = the partial sums of its lanes, added in lane order */
+		for (uint32_t g = 1; g < (1u << p.gshift); g++) {
+			const uint32_t from = lane - lane_group() + g;
+			const float tr = __shfl_sync(kFull, acc_r, from);
+			const float tg = __shfl_sync(kFull, acc_g, from);
+			const float tb = __shfl_sync(kFull, acc_b, from);
+			if (lane_group() == 0u) {
+				acc_r += tr; acc_g += tg; acc_b += tb;
+			}
+		}
+		if (in_image && lane_group() == 0u) {
 			p.raster[3 * (size_t)pixel + 0] = acc_r;
 			p.raster[3 * (size_t)pixel + 1] = acc_g;
 			p.raster[3 * (size_t)pixel + 2] = acc_b;

@@ -35,12 +35,13 @@ constexpr int kNumCounters = 17;
  * ~min warp start, max warp end, sum of warp lifetimes, ~min time a warp found the queue empty */
 constexpr int kTimeStart = kNumCounters, kTimeEnd = kNumCounters + 1, kTimeBusy = kNumCounters + 2, kTimeDry = kNumCounters + 3;
 constexpr int kTotalCounters = kNumCounters + 4;
-#ifndef CRT_MICRO_PIXELS
-#define CRT_MICRO_PIXELS 2                 /* pixels per work unit in the final phase of a frame */
+#ifndef CRT_GI_LANES
+#define CRT_GI_LANES 4                     /* lanes that share the GI samples of one pixel (power of two; part of a frame's arithmetic) */
 #endif
-#ifndef CRT_MICRO_PER_WARP
-#define CRT_MICRO_PER_WARP 64              /* pixels per resident warp handed out that way */
+#ifndef CRT_TAPER_PIXELS
+#define CRT_TAPER_PIXELS 24                /* units of s pixels are handed out while more than s * this many pixels per resident warp remain */
 #endif
+constexpr int kPhases = 4;                 /* unit sizes 8, 4, 2, 1 pixels */
 #ifndef CRT_MIN_BLOCKS
 #define CRT_MIN_BLOCKS 2                   /* resident render blocks per SM the register budget is set for */
 #endif
@@ -58,11 +59,11 @@ struct RenderParams {
 	uint32_t tiles_x, tiles_y;
 	uint32_t num_local_tiles;       /* tiles of this shard */
 	uint32_t refill;                /* lanes fetch new shadow rays when fewer than this many are walking */
-	uint32_t fine_from;             /* local tiles from this index on are handed out as 8-pixel rows */
-	uint32_t micro_from;            /* units from this index on are `micro_pixels` pixels of a tile, tiles from micro_tile on */
-	uint32_t micro_tile;
-	uint32_t micro_pixels;          /* 1, 2 or 4 */
-	uint32_t num_units;             /* fine_from tiles + rows of the next tiles + micro units of the last tiles */
+	uint32_t gshift;                /* log2 of the lanes that trace one pixel (path-traced GI with several samples), else 0 */
+	uint32_t fine_pixels;           /* pixels per work unit: min(8, 32 >> gshift) neighbours in an 8x4 tile */
+	uint32_t phase_unit[kPhases];   /* phase i = units of fine_pixels >> i pixels: its first unit (0xffffffff: no such phase) ... */
+	uint32_t phase_tile[kPhases];   /* ... and its first local tile */
+	uint32_t num_units;
 	unsigned int *tile_counter;
 	uint32_t system_counter;        /* the counter is shared with other devices (peer / IPC mapping): system-scope atomics */
 	unsigned long long *counters;   /* kTotalCounters, instrumented instance only */
