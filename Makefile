@@ -14,7 +14,7 @@ HOST_SRCS := src/core/argv.c src/core/strhash.c src/core/system.c \
 CSRC := c-raytracer_b200/csrc
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 \
 	-Xcompiler -fPIC -Iinclude -I$(CSRC)
-DEVICE_SRCS := $(CSRC)/crt_api.cu $(CSRC)/crt_kernels.cu $(CSRC)/crt_post.cu $(CSRC)/bvh_build.cpp
+DEVICE_SRCS := $(CSRC)/crt_api.cu $(CSRC)/crt_kernels.cu $(CSRC)/crt_post.cu $(CSRC)/crt_bvh_device.cu $(CSRC)/bvh_build.cpp
 
 all: host device engine postprocess oracle
 

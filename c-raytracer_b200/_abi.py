@@ -8,6 +8,7 @@ import ctypes as C
 import numpy as np
 
 CRT_ABI_VERSION = 2
+CRT_BUILD_HOST, CRT_BUILD_DEVICE = 0, 1
 
 CRT_OBJ_SPHERE, CRT_OBJ_TRIANGLE, CRT_OBJ_PLANE = 0, 1, 2
 CRT_TEX_UNIFORM, CRT_TEX_CHECKERBOARD, CRT_TEX_BRICK, CRT_TEX_NOISY_PERIODIC = 0, 1, 2, 3
@@ -46,7 +47,7 @@ class SceneDesc(C.Structure):
     _fields_ = [
         ("abi_version", C.c_uint32), ("num_objects", C.c_uint32), ("objects", C.POINTER(Object)),
         ("num_materials", C.c_uint32), ("materials", C.POINTER(Material)),
-        ("ambient", f3), ("reserved", C.c_float),
+        ("ambient", f3), ("build", C.c_uint32),
     ]
 
 
@@ -59,7 +60,8 @@ class RenderOpts(C.Structure):
         ("attenuation", C.c_int32), ("attenuation_offset", C.c_float),
         ("seed", C.c_uint32), ("flags", C.c_uint32),
         ("shard_index", C.c_uint32), ("shard_count", C.c_uint32),
-        ("reserved", C.c_uint32 * 4),
+        ("lens_radius", C.c_float), ("focus_distance", C.c_float), ("lens_samples", C.c_uint32),
+        ("fog_density", C.c_float), ("fog_color", f3), ("reserved", C.c_uint32),
     ]
 
 
@@ -96,6 +98,7 @@ class SceneInfo(C.Structure):
         ("total_lights", C.c_uint32), ("num_nodes", C.c_uint32), ("max_depth", C.c_uint32),
         ("device", C.c_uint32), ("sm_count", C.c_uint32),
         ("build_ms", C.c_double), ("upload_ms", C.c_double), ("device_bytes", C.c_uint64),
+        ("built_on_device", C.c_uint32), ("reserved", C.c_uint32),
     ]
 
 

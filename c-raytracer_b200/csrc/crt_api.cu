@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "bvh_build.h"
+#include "crt_bvh_device.cuh"
 #include "crt_kernels.cuh"
 
 using namespace crt;
@@ -214,6 +215,7 @@ struct HostScene {
 	uint32_t num_objects = 0, num_bounded = 0, total_lights = 0, wide_nodes_count = 0, wide_depth = 0;
 	float ambient[3] = { 0.f, 0.f, 0.f };
 	double build_ms = 0.0;
+	bool device_build = false; /* prims are in scene order, no tree: crt_bvh_device.cu builds it after the upload */
 };
 
 static int build_host_scene(const crt_scene_desc *desc, HostScene &h)
@@ -274,8 +276,13 @@ static int build_host_scene(const crt_scene_desc *desc, HostScene &h)
 
 	/* ---- BVH over the bounded objects ------------------------------------- */
 	const double t0 = now_ms();
-	std::vector<Aabb> boxes(bounded.size());
-	for (size_t k = 0; k < bounded.size(); k++) {
+	h.device_build = desc->build == CRT_BUILD_DEVICE;
+	if (const char *e = std::getenv("CRT_BVH_BUILD")) /* tools / tests: override the caller's choice */
+		h.device_build = std::strcmp(e, "device") == 0;
+	if (bounded.size() > kWideMaxPrims)
+		return fail(CRT_ERR_UNSUPPORTED, "scene too large for the device tree (%zu primitives)", bounded.size());
+	std::vector<Aabb> boxes(h.device_build ? 0 : bounded.size());
+	for (size_t k = 0; k < boxes.size(); k++) {
 		const crt_object &o = desc->objects[bounded[k]];
 		Aabb &b = boxes[k];
 		for (int a = 0; a < 3; a++) {
@@ -294,10 +301,12 @@ static int build_host_scene(const crt_scene_desc *desc, HostScene &h)
 		}
 	}
 	BvhResult bvh;
-	build_bvh(boxes, bvh);
-	/* the device tree: 8-wide collapse of the binary tree, one primitive per leaf slot, half-precision child boxes */
 	WideTree wide;
-	build_wide(boxes, bvh, wide);
+	if (!h.device_build) {
+		build_bvh(boxes, bvh);
+		/* the device tree: 8-wide collapse of the binary tree, one primitive per leaf slot, half-precision child boxes */
+		build_wide(boxes, bvh, wide);
+	}
 	if (wide.max_depth > kWideMaxDepth || wide.nodes.size() > kWideMaxNodes || bounded.size() > kWideMaxPrims)
 		return fail(CRT_ERR_UNSUPPORTED, "scene too large for the device tree (%zu nodes, %zu primitives, %u levels)",
 			wide.nodes.size(), bounded.size(), wide.max_depth);
@@ -307,7 +316,7 @@ static int build_host_scene(const crt_scene_desc *desc, HostScene &h)
 	h.prims.resize(4 * bounded.size());
 	h.slot_object.resize(bounded.size());
 	for (size_t slot = 0; slot < bounded.size(); slot++) {
-		const uint32_t oi = bounded[wide.order[slot]];
+		const uint32_t oi = bounded[h.device_build ? slot : wide.order[slot]];
 		const crt_object &o = desc->objects[oi];
 		const crt_material &m = mats[o.material];
 		uint32_t info = static_cast<uint32_t>(o.material) | ((m.flags & CRT_MAT_TRANSPARENT) ? PRIM_TRANSPARENT : 0u);
@@ -355,6 +364,31 @@ static int upload_host_scene(const HostScene &h, int device, crt_scene **out)
 	if (!rc) rc = upload(s, h.prims, &s->d.prims);
 	if (!rc) rc = upload(s, h.planes, &s->d.planes);
 	if (!rc) rc = upload(s, h.obj_slot, &s->d.obj_slot);
+	uint32_t nodes_count = h.wide_nodes_count, depth = h.wide_depth;
+	double build_ms = h.build_ms;
+	if (!rc && h.device_build && h.num_bounded) {
+		/* Morton codes, sort, radix tree, boxes, 8-wide collapse and the permutation of the records: all here */
+		const double tb = now_ms();
+		float4 *sorted = nullptr;
+		if (cudaMalloc(&sorted, h.prims.size() * sizeof(float4)) != cudaSuccess)
+			rc = fail(CRT_ERR_CUDA, "cudaMalloc(primitive records) failed");
+		DeviceTree tree;
+		if (!rc) {
+			s->allocs.push_back(sorted);
+			rc = build_device_tree(s->d.prims, h.num_bounded, const_cast<int32_t *>(s->d.obj_slot), sorted, tree);
+		}
+		if (!rc) {
+			s->allocs.push_back(tree.wide);
+			s->d.wide = tree.wide;
+			s->wide_bytes = static_cast<size_t>(tree.num_nodes) * sizeof(WideNode);
+			s->info.device_bytes += s->wide_bytes;
+			s->d.prims = sorted; /* the scene-order copy stays in allocs and goes with the scene */
+			nodes_count = tree.num_nodes;
+			depth = tree.max_depth;
+			build_ms += now_ms() - tb;
+			s->info.built_on_device = 1;
+		}
+	}
 	if (!rc) rc = upload(s, h.emitters, &s->d.emitters);
 	if (!rc) rc = upload(s, h.mats, &s->d.materials);
 	if (!rc && cudaMalloc(&s->tile_counter, sizeof(unsigned int)) != cudaSuccess)
@@ -367,8 +401,8 @@ static int upload_host_scene(const HostScene &h, int device, crt_scene **out)
 		crt_scene_destroy(s);
 		return rc;
 	}
-	s->d.num_nodes = h.wide_nodes_count;
-	s->wide_depth = h.wide_depth;
+	s->d.num_nodes = nodes_count;
+	s->wide_depth = depth;
 	s->d.num_prims = h.num_bounded;
 	s->d.num_planes = static_cast<uint32_t>(h.planes.size() / 2);
 	s->d.num_emitters = static_cast<uint32_t>(h.emitters.size());
@@ -376,14 +410,14 @@ static int upload_host_scene(const HostScene &h, int device, crt_scene **out)
 	s->d.total_lights = h.total_lights;
 	std::memcpy(s->d.ambient, h.ambient, sizeof s->d.ambient);
 
-	s->info.build_ms = h.build_ms;
-	s->info.upload_ms = now_ms() - t1;
+	s->info.build_ms = build_ms;
+	s->info.upload_ms = now_ms() - t1 - (build_ms - h.build_ms);
 	s->info.num_bounded = s->d.num_prims;
 	s->info.num_planes = s->d.num_planes;
 	s->info.num_emitters = s->d.num_emitters;
 	s->info.total_lights = h.total_lights;
 	s->info.num_nodes = s->d.num_nodes;
-	s->info.max_depth = h.wide_depth;
+	s->info.max_depth = depth;
 	s->info.device = static_cast<uint32_t>(device);
 	s->info.sm_count = static_cast<uint32_t>(s->sm_count);
 	*out = s;
@@ -408,6 +442,21 @@ int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out)
 	return upload_host_scene(h, device, out);
 }
 
+int crt_scene_read_tree(crt_scene *s, void *nodes, size_t nodes_bytes, void *prims, size_t prims_bytes)
+{
+	if (!s || (nodes_bytes && !nodes) || (prims_bytes && !prims))
+		return fail(CRT_ERR_INVALID, "NULL argument");
+	const size_t have_nodes = static_cast<size_t>(s->d.num_nodes) * sizeof(WideNode), have_prims = static_cast<size_t>(s->d.num_prims) * 64u;
+	if (nodes_bytes > have_nodes || prims_bytes > have_prims)
+		return fail(CRT_ERR_INVALID, "the tree has %zu bytes of nodes and %zu bytes of primitive records", have_nodes, have_prims);
+	CUDA_TRY(cudaSetDevice(s->device));
+	if (nodes_bytes)
+		CUDA_TRY(cudaMemcpy(nodes, s->d.wide, nodes_bytes, cudaMemcpyDeviceToHost));
+	if (prims_bytes)
+		CUDA_TRY(cudaMemcpy(prims, s->d.prims, prims_bytes, cudaMemcpyDeviceToHost));
+	return CRT_OK;
+}
+
 int crt_scene_get_info(const crt_scene *s, crt_scene_info *info)
 {
 	if (!s || !info)
@@ -421,12 +470,18 @@ int crt_render_device(crt_scene *s, const crt_render_opts *opts, float *d_raster
 	return crt_render_device_shared(s, opts, d_raster, d_z, cuda_stream, nullptr);
 }
 
+/* lens or fog asked for: the kernel instance that has them (crt_kernels.cu, EXT) */
+static bool uses_extensions(const crt_render_opts &o)
+{
+	return (o.lens_radius > 0.f && o.lens_samples > 1u) || o.fog_density > 0.f;
+}
+
 int crt_scene_resident_warps(crt_scene *s, const crt_render_opts *opts, uint32_t *warps)
 {
 	if (!s || !warps)
 		return fail(CRT_ERR_INVALID, "NULL argument");
 	CUDA_TRY(cudaSetDevice(s->device));
-	const int per_sm = render_blocks_per_sm(opts && (opts->flags & CRT_RENDER_COUNT_STATS));
+	const int per_sm = render_blocks_per_sm(opts && (opts->flags & CRT_RENDER_COUNT_STATS), opts && uses_extensions(*opts));
 	if (per_sm <= 0)
 		return fail(CRT_ERR_CUDA, "render kernel cannot be resident (%s)", cudaGetErrorString(cudaGetLastError()));
 	*warps = static_cast<uint32_t>(per_sm * s->sm_count * kWarpsPerBlock);
@@ -448,6 +503,11 @@ int crt_render_device_shared(crt_scene *s, const crt_render_opts *opts, float *d
 		return fail(CRT_ERR_INVALID, "too many samples per pixel");
 	if (opts->max_bounces > kMaxBounces)
 		return fail(CRT_ERR_INVALID, "max_bounces %u exceeds the supported %u", opts->max_bounces, kMaxBounces);
+	if (!(opts->lens_radius >= 0.f) || !std::isfinite(opts->lens_radius) || opts->lens_samples > 65536u ||
+		(opts->lens_radius > 0.f && opts->lens_samples > 1u && !(opts->focus_distance > 0.f && std::isfinite(opts->focus_distance))))
+		return fail(CRT_ERR_INVALID, "thin lens: needs a finite radius >= 0, a focus distance > 0 and at most 65536 samples");
+	if (!(opts->fog_density >= 0.f) || !std::isfinite(opts->fog_density))
+		return fail(CRT_ERR_INVALID, "fog: needs a finite density >= 0");
 	/* the per-frame scratch (work counter, pending stacks, contribution slots, events) belongs to
 	 * the scene: one frame in flight per crt_scene (see the stream wait below) */
 	CUDA_TRY(cudaSetDevice(s->device));
@@ -459,7 +519,8 @@ int crt_render_device_shared(crt_scene *s, const crt_render_opts *opts, float *d
 	const bool count = (opts->flags & CRT_RENDER_COUNT_STATS) != 0;
 
 	/* persistent grid: every resident warp slot of the device */
-	const int per_sm = render_blocks_per_sm(count);
+	const bool ext = uses_extensions(*opts);
+	const int per_sm = render_blocks_per_sm(count, ext);
 	if (per_sm <= 0)
 		return fail(CRT_ERR_CUDA, "render kernel cannot be resident (%s)", cudaGetErrorString(cudaGetLastError()));
 	const int grid = per_sm * s->sm_count;
@@ -589,7 +650,7 @@ int crt_render_device_shared(crt_scene *s, const crt_render_opts *opts, float *d
 	}
 	CUDA_TRY(cudaEventRecord(s->ev_start, stream));
 	launch_raygen_rows(*opts, s->row_pos, stream);
-	launch_render(p, grid, count, stream);
+	launch_render(p, grid, count, ext, stream);
 	CUDA_TRY(cudaEventRecord(s->ev_stop, stream));
 	CUDA_TRY(cudaGetLastError());
 	s->last_stream = stream;

@@ -146,6 +146,33 @@ __device__ __forceinline__ void gi_direction(float nx, float ny, float nz, bool 
 	dz = (-nx * nz * mul) * sx + nz * sy + (1.f - nz * nz * mul) * sz;
 }
 
+/* Thin lens: moves the primary ray's origin to a point of the lens disk (uniform, two draws of the
+ * ray's own stream far above those of the lights and the GI samples) and aims it at the point where
+ * the pinhole ray crosses the plane in focus.  vx x vy is the viewing direction (camera.c:30-32). */
+__device__ __forceinline__ void lens_ray(const crt_render_opts &o, Pending &r)
+{
+	float fx = o.vx[1] * o.vy[2] - o.vx[2] * o.vy[1], fy = o.vx[2] * o.vy[0] - o.vx[0] * o.vy[2], fz = o.vx[0] * o.vy[1] - o.vx[1] * o.vy[0];
+	const float finv = rsqrtf(fx * fx + fy * fy + fz * fz);
+	fx *= finv; fy *= finv; fz *= finv;
+	float along = r.dx * fx + r.dy * fy + r.dz * fz;
+	if (!(fabsf(along) > 1e-6f))
+		return;
+	const float ft = o.focus_distance / along;
+	const float px = r.ox + r.dx * ft, py = r.oy + r.dy * ft, pz = r.oz + r.dz * ft;
+	const float xinv = rsqrtf(o.vx[0] * o.vx[0] + o.vx[1] * o.vx[1] + o.vx[2] * o.vx[2]);
+	const float yinv = rsqrtf(o.vy[0] * o.vy[0] + o.vy[1] * o.vy[1] + o.vy[2] * o.vy[2]);
+	const float rad = o.lens_radius * sqrtf(crt_rand(r.node, 0xfffffff0u)), phi = 6.2831853f * crt_rand(r.node, 0xfffffff1u);
+	float sn, cs;
+	sincosf(phi, &sn, &cs);
+	const float a = rad * cs * xinv, b = rad * sn * yinv;
+	r.ox += a * o.vx[0] + b * o.vy[0];
+	r.oy += a * o.vx[1] + b * o.vy[1];
+	r.oz += a * o.vx[2] + b * o.vy[2];
+	const float dx = px - r.ox, dy = py - r.oy, dz = pz - r.oz;
+	const float dinv = rsqrtf(dx * dx + dy * dy + dz * dz);
+	r.dx = dx * dinv; r.dy = dy * dinv; r.dz = dz * dinv;
+}
+
 template <bool COUNT>
 __device__ __forceinline__ void flush_counters(const RenderParams &p, Counters &cn)
 {
@@ -169,7 +196,9 @@ __device__ __forceinline__ unsigned long long device_clock_ns()
 	return t;
 }
 
-template <bool COUNT>
+/* EXT: the instance with the in-tracer lens and fog (crt_render_opts.lens_* / fog_*); the frames of the
+ * reference's own options run the instance without a trace of them */
+template <bool COUNT, bool EXT>
 __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(const RenderParams p)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -234,6 +263,10 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 
 		float acc_r = 0.f, acc_g = 0.f, acc_b = 0.f, z_value = 0.f;
 		uint32_t sp = 0;
+		/* thin lens (crt_render_opts.lens_*, an extension): a pixel is the mean of lens_n primary rays, traced one
+		 * after the other; lens sample 0 is the reference's pinhole ray */
+		const uint32_t lens_n = EXT && o.lens_radius > 0.f && o.lens_samples > 1u ? o.lens_samples : 1u;
+		for (uint32_t ls = 0; ls < lens_n; ls++) {
 		bool primary = true;
 
 		if (in_image) {
@@ -249,8 +282,10 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 			r.kr = r.kg = r.kb = 1.f;
 			r.remaining = o.max_bounces;
 			r.inside = -1;
-			r.node = crt_node_root(o.seed, pixel);
+			r.node = crt_node_root(EXT ? o.seed + 0x9e3779b9u * ls : o.seed, pixel);
 			r.aux = 0;
+			if (EXT && ls > 0u)
+				lens_ray(o, r);
 			pending_store(pending_slot(p, warp_global, sp++, lane), r);
 		}
 
@@ -315,6 +350,10 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 				hit.slot = __shfl_sync(kFull, hit.slot, lead);
 			}
 			const bool is_hit = have && hit.object >= 0;
+			if (EXT && o.fog_density > 0.f && have && !is_hit && ray.dx == ray.dx && !(primary && lane_group() != 0u)) {
+				/* a segment that leaves the scene ends in fog */
+				acc_r += o.fog_color[0] * r.kr; acc_g += o.fog_color[1] * r.kg; acc_b += o.fog_color[2] * r.kb;
+			}
 
 			/* ---- shading set-up (render.c:155-168) ------------------------- */
 			float nx = 0.f, ny = 0.f, nz = 0.f, bdot = 0.f, eps = 0.f;
@@ -336,6 +375,15 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 				outside = signbit(bdot);
 				const float att = eye_attenuation(o, hit.t);
 				wr = r.kr * att; wg = r.kg * att; wb = r.kb * att;
+				if (EXT && o.fog_density > 0.f) { /* in-tracer fog (extension): the segment keeps T of what it carries */
+					const float T = __expf(-o.fog_density * hit.t);
+					if (!ghost) {
+						acc_r += o.fog_color[0] * r.kr * (1.f - T);
+						acc_g += o.fog_color[1] * r.kg * (1.f - T);
+						acc_b += o.fog_color[2] * r.kb * (1.f - T);
+					}
+					wr *= T; wg *= T; wb *= T;
+				}
 				/* emission + ambient term (render.c:164, :233-237) */
 				float cr = __ldg(&m->ke[0]), cg = __ldg(&m->ke[1]), cb = __ldg(&m->ke[2]);
 				if (o.gi_model == CRT_GI_AMBIENT) {
@@ -346,7 +394,7 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 				if (!ghost) {
 					acc_r += cr * wr; acc_g += cg * wg; acc_b += cb * wb;
 				}
-				if (primary && !ghost && o.max_bounces > 0u)
+				if (primary && (!EXT || ls == 0u) && !ghost && o.max_bounces > 0u)
 					z_value = hit.t; /* render.c:304-305, :342 */
 				/* is the hit object itself an emitter? it is skipped as a light (render.c:172) */
 				uint32_t lights = sc.total_lights;
@@ -580,6 +628,8 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 				if (r.remaining > 0u) {
 					const bool ghost = primary && lane_group() != 0u;
 					const crt_material *m = sc.materials + mat_index;
+					/* fog: what the children bring back crosses this segment as well (recomputed, not kept in a register) */
+					const float fogT = EXT && o.fog_density > 0.f ? __expf(-o.fog_density * hit.t) : 1.f;
 					const uint32_t flags = __ldg(&m->flags);
 					uint32_t n_gi = 0;
 					if (o.gi_model == CRT_GI_PATH && outside)
@@ -590,6 +640,9 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 					if (!ghost && r.inside != hit.object && (flags & CRT_MAT_REFLECTIVE)) {
 						/* render.c:308-317 */
 						rr.kr = r.kr * __ldg(&m->kr[0]); rr.kg = r.kg * __ldg(&m->kr[1]); rr.kb = r.kb * __ldg(&m->kr[2]);
+						if (EXT && o.fog_density > 0.f) {
+							rr.kr *= fogT; rr.kg *= fogT; rr.kb *= fogT;
+						}
 						if (o.min_intensity_sqr < xdot(rr.kr, rr.kg, rr.kb, rr.kr, rr.kg, rr.kb)) {
 							spawn_r = true;
 							const float b2 = xmul(2.f, bdot);
@@ -604,6 +657,9 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 					if (!ghost && (flags & CRT_MAT_TRANSPARENT)) {
 						/* refraction by explicit angles (render.c:320-340) */
 						rt.kr = r.kr * __ldg(&m->kt[0]); rt.kg = r.kg * __ldg(&m->kt[1]); rt.kb = r.kb * __ldg(&m->kt[2]);
+						if (EXT && o.fog_density > 0.f) {
+							rt.kr *= fogT; rt.kg *= fogT; rt.kb *= fogT;
+						}
 						if (o.min_intensity_sqr < xdot(rt.kr, rt.kg, rt.kb, rt.kr, rt.kg, rt.kb)) {
 							spawn_t = true;
 							const float ior = __ldg(&m->refractive_index);
@@ -657,7 +713,12 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 			}
 			primary = false;
 		}
+		} /* lens samples */
 
+		if (EXT && lens_n > 1u) { /* the mean over the lens; the rays keep unit weight so that -a cuts them where it would cut the pinhole ray */
+			const float inv = 1.f / (float)lens_n;
+			acc_r *= inv; acc_g *= inv; acc_b *= inv;
+		}
 		/* a pixel = the partial sums of its lanes, added in lane order */
 		for (uint32_t g = 1; g < (1u << p.gshift); g++) {
 			const uint32_t from = lane - lane_group() + g;
@@ -782,25 +843,34 @@ void launch_raygen_rows(const crt_render_opts &o, float *row_pos, cudaStream_t s
 
 constexpr size_t kRenderSmem = (sizeof(WarpShared) + sizeof(uint32_t) * kLaneStackWords * 32) * kWarpsPerBlock;
 
-int render_blocks_per_sm(bool count)
+template <bool COUNT, bool EXT>
+static int blocks_per_sm_of()
 {
 	int n = 0;
-	if (count) {
-		cudaFuncSetAttribute(render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRenderSmem);
-		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_kernel<true>, kBlockThreads, kRenderSmem);
-	} else {
-		cudaFuncSetAttribute(render_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRenderSmem);
-		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_kernel<false>, kBlockThreads, kRenderSmem);
-	}
+	cudaFuncSetAttribute(render_kernel<COUNT, EXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRenderSmem);
+	cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_kernel<COUNT, EXT>, kBlockThreads, kRenderSmem);
 	return n;
 }
 
-void launch_render(const RenderParams &p, int grid, bool count, cudaStream_t stream)
+int render_blocks_per_sm(bool count, bool ext)
 {
-	if (count)
-		render_kernel<true><<<grid, kBlockThreads, kRenderSmem, stream>>>(p);
-	else
-		render_kernel<false><<<grid, kBlockThreads, kRenderSmem, stream>>>(p);
+	if (ext)
+		return count ? blocks_per_sm_of<true, true>() : blocks_per_sm_of<false, true>();
+	return count ? blocks_per_sm_of<true, false>() : blocks_per_sm_of<false, false>();
+}
+
+void launch_render(const RenderParams &p, int grid, bool count, bool ext, cudaStream_t stream)
+{
+	if (ext) {
+		if (count)
+			render_kernel<true, true><<<grid, kBlockThreads, kRenderSmem, stream>>>(p);
+		else
+			render_kernel<false, true><<<grid, kBlockThreads, kRenderSmem, stream>>>(p);
+	} else if (count) {
+		render_kernel<true, false><<<grid, kBlockThreads, kRenderSmem, stream>>>(p);
+	} else {
+		render_kernel<false, false><<<grid, kBlockThreads, kRenderSmem, stream>>>(p);
+	}
 }
 
 void launch_trace_closest(const DScene &sc, const float *rays, size_t n, int32_t *object, float *t, float *normal, cudaStream_t stream)

@@ -76,8 +76,9 @@ struct RenderParams {
 
 /* grid = number of persistent blocks */
 void launch_raygen_rows(const crt_render_opts &o, float *row_pos, cudaStream_t stream);
-void launch_render(const RenderParams &p, int grid, bool count, cudaStream_t stream);
-int render_blocks_per_sm(bool count);
+/* ext: the instance with the lens / fog extensions of crt_render_opts */
+void launch_render(const RenderParams &p, int grid, bool count, bool ext, cudaStream_t stream);
+int render_blocks_per_sm(bool count, bool ext);
 
 void launch_trace_closest(const DScene &sc, const float *rays, size_t n, int32_t *object, float *t, float *normal, cudaStream_t stream);
 void launch_trace_shadow(const DScene &sc, const float *rays, const float *dist, const int32_t *emitter, size_t n,

@@ -19,7 +19,7 @@ SYMBOLS = [
     "crt_scene_create", "crt_scene_destroy", "crt_scene_get_info",
     "crt_render", "crt_render_device", "crt_render_device_sync",
     "crt_scene_resident_warps", "crt_render_device_shared",
-    "crt_shared_alloc", "crt_shared_open", "crt_shared_release", "crt_host_register", "crt_host_unregister",
+    "crt_shared_alloc", "crt_shared_open", "crt_shared_release", "crt_host_register", "crt_host_unregister", "crt_scene_read_tree",
     "crt_multi_create", "crt_multi_destroy", "crt_multi_num_devices", "crt_multi_is_dynamic", "crt_multi_get_info", "crt_multi_render",
     "crt_trace_closest", "crt_trace_shadow", "crt_texture_eval", "crt_measure_fp32_peak",
     "crt_postprocess", "crt_postprocess_device",
@@ -52,6 +52,7 @@ def lib():
         L.crt_shared_alloc.argtypes = [C.c_int, C.c_size_t, C.POINTER(C.c_void_p), C.c_void_p]
         L.crt_shared_open.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
         L.crt_shared_release.argtypes = [C.c_int, C.c_void_p, C.c_int]
+        L.crt_scene_read_tree.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
         L.crt_host_register.argtypes = [C.c_void_p, C.c_size_t]
         L.crt_host_unregister.argtypes = [C.c_void_p]
         L.crt_multi_create.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
@@ -110,13 +111,26 @@ class DeviceScene:
     """A scene resident on one GPU (crt_scene*).  `scene` is a host.Scene or
     anything exposing a `desc` (_abi.SceneDesc)."""
 
-    def __init__(self, scene, device=0):
+    def __init__(self, scene, device=0, build=None):
+        """build: None (what scene.desc says: the host), "host" or "device" (crt_scene_desc.build)."""
         self.scene = scene
         h = C.c_void_p()
-        _check(lib().crt_scene_create(C.addressof(scene.desc), device, C.byref(h)))
+        desc = scene.desc
+        if build is not None:
+            desc = _abi.SceneDesc.from_buffer_copy(scene.desc)
+            desc.build = {"host": _abi.CRT_BUILD_HOST, "device": _abi.CRT_BUILD_DEVICE}[build]
+        _check(lib().crt_scene_create(C.addressof(desc), device, C.byref(h)))
         self._h = h
         self.info = _abi.SceneInfo()
         _check(lib().crt_scene_get_info(self._h, C.addressof(self.info)))
+
+    def read_tree(self):
+        """(nodes, prims): the device tree as numpy arrays -- nodes (num_nodes, 32) uint32 words of the
+        128-byte records, prims (num_bounded, 16) float32."""
+        nodes = np.empty((self.info.num_nodes, 32), dtype=np.uint32)
+        prims = np.empty((self.info.num_bounded, 16), dtype=np.float32)
+        _check(lib().crt_scene_read_tree(self._h, nodes.ctypes.data, nodes.nbytes, prims.ctypes.data, prims.nbytes))
+        return nodes, prims
 
     def close(self):
         if getattr(self, "_h", None):

@@ -136,8 +136,13 @@ typedef struct crt_scene_desc {
 	uint32_t num_materials;
 	const crt_material *materials;
 	float ambient[3]; /* "AmbientLight", scene.c:104-105 */
-	float reserved;
+	uint32_t build;   /* enum crt_build: where accel_init()'s tree is built */
 } crt_scene_desc;
+
+/* CRT_BUILD_HOST: binned-SAH tree on one host core, uploaded (fewest box tests per ray; 0.2-0.5 s for a
+ * million triangles).  CRT_BUILD_DEVICE: Morton codes + sort + radix tree on the device in milliseconds
+ * (accel.c:72-88, 227-264 as it was meant); more box tests per ray.  Same images. */
+enum crt_build { CRT_BUILD_HOST = 0, CRT_BUILD_DEVICE = 1 };
 
 enum crt_reflection_model { CRT_REFLECTION_PHONG = 0, CRT_REFLECTION_BLINN = 1 };
 enum crt_gi_model { CRT_GI_AMBIENT = 0, CRT_GI_PATH = 1 };
@@ -176,7 +181,22 @@ typedef struct crt_render_opts {
 	/* Multi-GPU sharding: tile-chunk k is rendered iff k % shard_count ==
 	 * shard_index.  Pixels of other shards are left zero.  (1-rank: 0 / 1.) */
 	uint32_t shard_index, shard_count;
-	uint32_t reserved[4];
+	/* In-tracer thin lens and fog.  EXTENSIONS: the reference has neither (its depth of
+	 * field and mist are post-processes on the z-buffer, postproc.c:47-188 = crt_postprocess), so there is
+	 * no parity oracle for them; all zero = the reference's pinhole camera in clear air, bit for bit.
+	 *   lens_radius > 0: the primary ray of lens sample s starts at a point of the lens disk (spanned by
+	 *     vx, vy around cam_pos) and passes through the point the pinhole ray meets the plane at
+	 *     focus_distance in front of the camera; a pixel is the mean of lens_samples such rays
+	 *     (sample 0 is the pinhole ray itself and writes the z-buffer).
+	 *   fog_density > 0: every eye-path segment of length t (primary, reflected, refracted, GI) keeps
+	 *     exp(-fog_density * t) of what it carries and gains (1 - exp(..)) of fog_color; a segment that
+	 *     leaves the scene carries fog_color. */
+	float lens_radius;
+	float focus_distance;
+	uint32_t lens_samples; /* 0 or 1: one ray per pixel */
+	float fog_density;
+	float fog_color[3];
+	uint32_t reserved;
 } crt_render_opts;
 
 /* Counters of one crt_render call (all zero unless CRT_RENDER_COUNT_STATS). */
@@ -216,6 +236,8 @@ typedef struct crt_scene_info {
 	double build_ms;       /* host BVH build */
 	double upload_ms;
 	uint64_t device_bytes;
+	uint32_t built_on_device; /* 1: CRT_BUILD_DEVICE was used (build_ms is device + sync time) */
+	uint32_t reserved;
 } crt_scene_info;
 
 const char *crt_last_error(void);
@@ -227,6 +249,11 @@ int crt_device_count(void);
 int crt_scene_create(const crt_scene_desc *desc, int device, crt_scene **out);
 void crt_scene_destroy(crt_scene *scene);
 int crt_scene_get_info(const crt_scene *scene, crt_scene_info *info);
+/* Diagnostics: the acceleration structure as the kernels read it -- info.num_nodes records of 128 bytes
+ * (c-raytracer_b200/csrc/bvh_build.h, WideNode) and info.num_bounded primitive records of 64 bytes in tree
+ * order (v0.xyz eps | e0.xyz info | e1.xyz object | normal.xyz -; a sphere: centre eps | radius - - info).
+ * Copies the first nodes_bytes / prims_bytes bytes. */
+int crt_scene_read_tree(crt_scene *scene, void *nodes, size_t nodes_bytes, void *prims, size_t prims_bytes);
 
 /* Replaces render() (render.c:345-368).  raster = W*H*3 floats, z_buffer =
  * W*H floats, HOST memory, row-major top-left origin, fully overwritten

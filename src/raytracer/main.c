@@ -44,7 +44,13 @@ static const char *const HELP_EXTRA =
 	"B200 BUILD, ADDITIONAL PARAMETERS:\n"
 	"[--device] (integer)             : DEFAULT = 0       : CUDA device the trace loop runs on ([-m] is accepted and ignored).\n"
 	"[--gpus] (integer | \"max\")       : DEFAULT = 1       : number of CUDA devices that share the frame (devices 0 .. N-1).\n"
+	"[--bvh] (host | device)          : DEFAULT = host    : where the acceleration structure is built: binned SAH on a host core, or Morton codes + radix tree on the device.\n"
 	"[--devices] (list)               : DEFAULT = none    : comma-separated CUDA devices that share the frame, e.g. 0,2,3.\n"
+	"[--lens-radius] (decimal)        : DEFAULT = 0       : thin-lens camera: radius of the lens (0 = the reference's pinhole).\n"
+	"[--focus] (decimal)              : DEFAULT = 0       : thin-lens camera: distance of the plane in focus.\n"
+	"[--lens-samples] (integer)       : DEFAULT = 1       : thin-lens camera: primary rays per pixel.\n"
+	"[--fog] (decimal)                : DEFAULT = 0       : in-tracer fog: extinction per unit length along every eye-path segment.\n"
+	"[--fog-color] (r,g,b)            : DEFAULT = 0,0,0   : in-tracer fog: colour gained where light is lost.\n"
 	"[--seed] (integer)               : DEFAULT = 1       : seed of the counter-based sampling stream.\n"
 	"[--stats]                        : DEFAULT = OFF     : count rays and intersection tests, print Mrays/s.\n";
 
@@ -73,6 +79,9 @@ int main(int argc, char *argv[])
 	if (rt_scene_load(argv[RT_ARG_SCENE], r ? argv[r + 1] : NULL, &scene, err))
 		rt_fatal("%s", err);
 	rt_log("Loaded %zu materials, %zu objects.", scene.num_materials, scene.num_objects);
+	const int bv = rt_args_find_with_values(&args, "--bvh", 1);
+	if (bv && !strcmp(argv[bv + 1], "device"))
+		scene.build = CRT_BUILD_DEVICE;
 
 	rt_log("Initializing image.");
 	struct rt_image image;
@@ -122,8 +131,8 @@ int main(int argc, char *argv[])
 	} else if (rt_render(&scene, &image, &opts, num_devices == 1 ? devices[0] : device, &stats, &info, err)) {
 		rt_fatal("%s", err);
 	}
-	rt_log("BVH: %u nodes over %u primitives, depth %u, built in %.1f ms; trace kernel %.3f ms, call %.3f ms.",
-		info.num_nodes, info.num_bounded, info.max_depth, info.build_ms, stats.kernel_ms, stats.total_ms);
+	rt_log("BVH: %u nodes over %u primitives, depth %u, built on the %s in %.1f ms; trace kernel %.3f ms, call %.3f ms.",
+		info.num_nodes, info.num_bounded, info.max_depth, info.built_on_device ? "device" : "host", info.build_ms, stats.kernel_ms, stats.total_ms);
 	if (opts.flags & CRT_RENDER_COUNT_STATS) {
 		const double rays = (double)(stats.rays_closest + stats.rays_shadow);
 		rt_log("Rays: %llu closest-hit + %llu shadow = %.1f Mrays/s; %.1f box tests per ray.",

@@ -4,6 +4,7 @@
  */
 #include "render.h"
 
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -70,6 +71,20 @@ void rt_render_parse(crt_render_opts *o, const struct rt_args *args)
 		o->seed = (uint32_t)strtoul(v, NULL, 10);
 	if (rt_args_find(args, "--stats"))
 		o->flags |= CRT_RENDER_COUNT_STATS;
+	/* extensions without a counterpart in the reference (include/crt.h): off unless asked for */
+	if ((v = value_of(args, "--lens-radius")))
+		o->lens_radius = (float)atof(v);
+	if ((v = value_of(args, "--focus")))
+		o->focus_distance = (float)atof(v);
+	if ((v = value_of(args, "--lens-samples")))
+		o->lens_samples = (uint32_t)abs(atoi(v));
+	if ((v = value_of(args, "--fog")))
+		o->fog_density = (float)atof(v);
+	if ((v = value_of(args, "--fog-color"))) {
+		float c[3] = { 0.f, 0.f, 0.f };
+		if (sscanf(v, "%f,%f,%f", &c[0], &c[1], &c[2]) == 3)
+			v3_copy(o->fog_color, c);
+	}
 }
 
 void rt_render_set_view(crt_render_opts *o, const struct rt_scene *scene, const struct rt_image *img)

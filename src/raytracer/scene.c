@@ -353,6 +353,7 @@ void rt_scene_desc(const struct rt_scene *sc, crt_scene_desc *desc)
 	desc->num_materials = (uint32_t)sc->num_materials;
 	desc->materials = sc->materials;
 	v3_copy(desc->ambient, sc->ambient);
+	desc->build = sc->build;
 }
 
 static char *slurp(const char *filename, char *err)

@@ -19,6 +19,7 @@ struct rt_scene {
 	size_t num_emitters;
 	size_t num_planes;
 	float ambient[3];
+	uint32_t build; /* enum crt_build (--bvh host | device); 0 after rt_scene_load() */
 };
 
 /* rescale: NULL, "norm" (1 / largest extent) or a decimal factor: the -r flag
