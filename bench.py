@@ -393,23 +393,21 @@ def ours(a):
     # DRAM bytes per launch of this kernel from the committed ncu capture of this very workload (not measured live)
     traffic = None
     try:
-        import hashlib
         t = json.load(open(os.path.join(ROOT, "profiles", "dram_traffic.json")))
-        sha = hashlib.sha256(open(device.LIB_PATH, "rb").read()).hexdigest()
-        # only the capture of THIS build of libcrt.so on THIS workload counts
-        if t["workload"] == workload_name(a) and world == t["n_gpus"] and t.get("libcrt_sha256") == sha:
+        # only the capture of THESE device sources on THIS workload counts (libcrt.so is not reproducible bit for bit)
+        if t["workload"] == workload_name(a) and world == t["n_gpus"] and t.get("device_sources_sha256") == device.source_fingerprint():
             traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     except (OSError, KeyError, ValueError):
         pass
     roofline = {
         "bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
         "traffic": traffic,
-        "kernel": "render_kernel<false>", "kernel_ms": sum(kernel_ms) / len(kernel_ms),
+        "kernel": "render_kernel<false, false>", "kernel_ms": sum(kernel_ms) / len(kernel_ms),
         "peak_source": "measured live: crt_measure_fp32_peak (FFMA micro-kernel); nominal 148*128*2*1.965 GHz = 74.4",
         "flops_per_ray": total_flops / total_rays, "box_tests_per_ray": tot.box_tests / total_rays,
         "note": "algorithmic FLOPs by SURVEY 8(d): 3/ray + 12/box test + tri 14/24/40/46 + sphere 17/20 + plane 12; "
                 "HBM is not the bound (scene %.0f MB mostly L2-resident; traffic = DRAM bytes per launch from profiles/dram_traffic.json "
-                "when it was captured from this build of libcrt.so, else null; measured hbm peak %s GB/s)" % (info.device_bytes / 1e6, peaks.get("hbm_gbs")),
+                "when it was captured from these device sources, else null; measured hbm peak %s GB/s)" % (info.device_bytes / 1e6, peaks.get("hbm_gbs")),
     }
 
     line = {

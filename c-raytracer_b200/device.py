@@ -215,6 +215,22 @@ def shared_open(dev, handle):
     return p.value
 
 
+def source_fingerprint():
+    """SHA-256 over the sources libcrt.so is built from (csrc/, include/, the nvcc flags in the Makefile): the
+    library itself is not reproducible bit for bit, so profiles that belong to one build are tied to this."""
+    import hashlib
+    root = os.path.dirname(HERE)
+    files = sorted(os.path.join(HERE, "csrc", f) for f in os.listdir(os.path.join(HERE, "csrc")) if f.endswith((".cu", ".cuh", ".h", ".cpp")))
+    files += [os.path.join(root, "include", f) for f in sorted(os.listdir(os.path.join(root, "include")))]
+    h = hashlib.sha256()
+    for f in files:
+        h.update(os.path.basename(f).encode() + b"\0" + open(f, "rb").read())
+    for line in open(os.path.join(root, "Makefile")):
+        if line.startswith("NVFLAGS") or line.startswith("\t-Xcompiler"):
+            h.update(line.encode())
+    return h.hexdigest()
+
+
 def host_register(array):
     """crt_host_register on a numpy array the caller keeps alive; undo with host_unregister()."""
     _check(lib().crt_host_register(C.c_void_p(array.ctypes.data), array.nbytes))

@@ -460,3 +460,74 @@ def test_frames_enqueued_without_sync_are_ordered(gpu):
     np.testing.assert_array_equal(r1.cpu().numpy(), want1)
     np.testing.assert_array_equal(r2.cpu().numpy(), want2)
     np.testing.assert_array_equal(z2.cpu().numpy(), want_z2)
+
+
+def _flat_grid_stl(path, n, x0, y0, z0, cell):
+    """n x n axis-aligned quads (2 right triangles each) in the plane z = z0: every triangle's box is flat
+    and its legs lie on the box edges."""
+    import struct
+    tris = []
+    for i in range(n):
+        for j in range(n):
+            a = (x0 + i * cell, y0 + j * cell, z0)
+            b = (x0 + (i + 1) * cell, y0 + j * cell, z0)
+            c = (x0 + (i + 1) * cell, y0 + (j + 1) * cell, z0)
+            d = (x0 + i * cell, y0 + (j + 1) * cell, z0)
+            tris += [(a, b, c), (a, c, d)]
+    with open(path, "wb") as f:
+        f.write(b"\0" * 80 + struct.pack("<I", len(tris)))
+        for t in tris:
+            f.write(struct.pack("<3f", 0, 0, 1))
+            for v in t:
+                f.write(struct.pack("<3f", *v))
+            f.write(b"\0\0")
+    return np.array(tris, dtype=np.float64)
+
+
+def test_far_origins_and_flat_boxes(gpu, tmp_path):
+    """Rays from 10^2 .. 10^5 units away at axis-aligned flat triangles, aimed just inside their legs
+    (= the edges of their flat boxes): the rounding error of a slab test grows with the distance and the
+    origin, not with the box, so a walk without a ray-side margin culls true hits here.
+    The node test is conservative (crt_device.cuh wide_node_test: half-precision planes padded by
+    kWideSlack, the ray re-based to its entry point): every hit of the reference walk must be found."""
+    import json
+    tris = _flat_grid_stl(str(tmp_path / "grid.stl"), 24, 100.0, -37.0, 3.0, 0.125)
+    s = json.load(open(scene_path("scene1")))
+    s["Objects"] = [o for o in s["Objects"] if o["parameters"].get("lights")] + [
+        {"type": "Mesh", "parameters": {"material": s["Materials"][0]["id"], "filename": str(tmp_path / "grid.stl"),
+                                        "position": [0, 0, 0], "rotation": [0, 0, 0], "scale": 1}}]
+    p = tmp_path / "scene.json"
+    p.write_text(json.dumps(s))
+    sc = host.Scene(str(p))
+    rng = np.random.default_rng(5)
+    n = 120_000
+    t = tris[rng.integers(0, len(tris), n)]
+    # barycentric points hugging a leg or a vertex, and some well inside
+    eps = 10.0 ** rng.uniform(-5, -1, n)
+    u = np.where(rng.random(n) < 0.5, eps, rng.random(n) * 0.5)
+    v = np.where(rng.random(n) < 0.5, eps, (1 - u) * rng.random(n) * 0.9)
+    deep = (u > 0.05) & (v > 0.05) & (u + v < 0.9)
+    tgt = t[:, 0] + u[:, None] * (t[:, 1] - t[:, 0]) + v[:, None] * (t[:, 2] - t[:, 0])
+    dirs = rng.normal(size=(n, 3))
+    axis = rng.random(n) < 0.2          # one zero component: the ray runs parallel to two box faces' normals
+    dirs[axis, rng.integers(0, 2, axis.sum())] = 0.0
+    dirs[:, 2] = -np.abs(dirs[:, 2]) - 0.05  # towards the sheet from above
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    far = 10.0 ** rng.uniform(2, 5, n)
+    org = tgt - dirs * far[:, None]
+    rays = np.concatenate([dirs, org], axis=1).astype(np.float32)
+    orc = oracle.OracleScene(sc)
+    oo, ot, _ = orc.trace_closest(rays)
+    for build in ("host", "device"):
+        dev = device.DeviceScene(sc, 0, build=build)
+        go, gt, _ = dev.trace_closest(rays)
+        # object 0 is the scene's light, a sphere of radius 0.5: from 10^4.5 away its discriminant (b^2 - c near
+        # 2e9, ulp 256) is noise in both implementations, so only hits on the sheet are compared
+        found, wanted = go >= 0, oo >= 1
+        assert wanted.mean() > 0.5
+        assert not (wanted & ~found).any(), f"{build} tree: {int((wanted & ~found).sum())} hits of the reference walk culled"
+        both = found & wanted & (go == oo)
+        np.testing.assert_array_equal(gt[both], ot[both])
+        # the float32 ray misses its target by ~1e-7 * distance: points well inside a triangle are hit up to 10^4 away
+        sure = deep & (far < 1e4)
+        assert found[sure].all()
