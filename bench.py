@@ -54,6 +54,9 @@ def parse_args():
     ap.add_argument("--spp", type=int, default=16, help="-n: GI samples at the primary hit")
     ap.add_argument("--gi", default="path", choices=["path", "ambient"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--bvh", default="host", choices=["host", "device"],
+                    help="where the acceleration structure is built (crt_scene_desc.build): binned SAH on the host cores (fewest box tests "
+                         "per ray, the default) or Morton codes + radix tree on the GPU (milliseconds; a few percent slower frames)")
     ap.add_argument("--static-shards", action="store_true", help="N > 1: static tile shards + NCCL reduce instead of the shared work queue")
     ap.add_argument("--sample", default=f"{SAMPLE_W}x{SAMPLE_H}", help="frame size of the CPU-baseline sample")
     ap.add_argument("--ref-steps", type=int, default=1, help="--impl reference: timed runs of the sample (each is all host cores for tens of seconds)")
@@ -232,7 +235,7 @@ def ours(a):
 
     scene = host.Scene(os.path.join(ROOT, "scenes", a.scene + ".json"))
     t0 = time.time()
-    dev = device.DeviceScene(scene, local)
+    dev = device.DeviceScene(scene, local, build=a.bvh)
     setup_s = time.time() - t0
     W, H = a.width, a.height
     pixels = W * H
@@ -420,7 +423,7 @@ def ours(a):
             "l2": "flushed between steps (256 MiB memset)", "parallelism": (f"one dynamic work queue over {world} GPUs (crt_frame_share: 8-pixel units, system-scope atomics, "
                                                                           f"frame on rank 0 over CUDA IPC / NVLink), scene replicated" if dynamic else
                                                                           f"tile-chunk round-robin x{world}, scene replicated"),
-            "bvh_nodes": info.num_nodes, "bvh_build_ms": info.build_ms, "scene_upload_ms": info.upload_ms,
+            "bvh_nodes": info.num_nodes, "bvh_build_ms": info.build_ms, "bvh_built_on": "device" if info.built_on_device else "host", "scene_upload_ms": info.upload_ms,
             "scene_setup_s": setup_s, "seed": 1, "assemble_ms": assemble_ms, "assemble_alone_ms": assemble_alone_ms,
             "per_rank_ms": per_rank_ms,
         },
