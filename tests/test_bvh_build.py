@@ -30,3 +30,17 @@ def test_tree_invariants(checker, n, seed, kind):
     r = subprocess.run([checker, str(n), str(seed), str(kind)], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     assert r.stdout.startswith("ok")
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_node_test_is_conservative(tmp_path_factory, seed):
+    """The device's half-precision node test, emulated bit for bit on the CPU (tests/node_test_emu.cpp), never
+    misses a slot whose content the ray segment truly meets: random, axis-parallel, face / edge / corner grazing
+    from near and far, origins inside the node (with kWideSlack set to 0 the same program fails at once)."""
+    exe = str(tmp_path_factory.mktemp("emu") / "node_test_emu")
+    csrc = os.path.join(ROOT, "c-raytracer_b200", "csrc")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-I", csrc, os.path.join(ROOT, "tests", "node_test_emu.cpp"),
+                    os.path.join(csrc, "bvh_build.cpp"), "-o", exe, "-lpthread"], check=True)
+    r = subprocess.run([exe, "20000", "30000", str(seed)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.startswith("ok")
