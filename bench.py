@@ -398,7 +398,7 @@ def ours(a):
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "dram_traffic.json")))
         # only the capture of THESE device sources on THIS workload counts (libcrt.so is not reproducible bit for bit)
-        if t["workload"] == workload_name(a) and world == t["n_gpus"] and t.get("device_sources_sha256") == device.source_fingerprint():
+        if t["workload"] == workload_name(a) and world == t["n_gpus"] and not info.built_on_device and t.get("device_sources_sha256") == device.source_fingerprint():
             traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     except (OSError, KeyError, ValueError):
         pass

@@ -18,13 +18,15 @@ except Exception as e:
     print(sys.argv[1], "FAILED", e)
 PY
 }
-python -m pytest tests/test_gpu_multi.py -m gpu -q 2>&1 | tail -2
+# SCALE_FULL=1 adds the 2-device tests, the static-shard comparison and scene6 -n 256 (about twice the box time)
+[ -n "$SCALE_FULL" ] && python -m pytest tests/test_gpu_multi.py -m gpu -q 2>&1 | tail -2
+run scene5_2gpu 2 --steps 3 --warmup 3 --no-cpu-baseline
 run scene5_4gpu 4 --steps 5 --warmup 3
 run scene5_8gpu 8 --steps 5 --warmup 3
-run scene5_8gpu_static 8 --steps 5 --warmup 3 --static-shards
+[ -n "$SCALE_FULL" ] && run scene5_8gpu_static 8 --steps 5 --warmup 3 --static-shards
 run scene6_4k_n64_8gpu 8 --scene scene6 --width 3840 --height 2160 --spp 64 --steps 5 --warmup 3
-run scene6_4k_n256_8gpu 8 --scene scene6 --width 3840 --height 2160 --spp 256 --steps 3 --warmup 3
-for g in 1 8; do
+[ -n "$SCALE_FULL" ] && run scene6_4k_n256_8gpu 8 --scene scene6 --width 3840 --height 2160 --spp 256 --steps 3 --warmup 3
+for g in ${SCALE_ENGINE_GPUS:-8}; do
 	./engine scenes/scene6.json $out/${tag}_engine_$g.tif 3840 2160 -g path -n 64 --gpus $g > $out/${tag}_engine_scene6_4k_${g}gpu.log 2>&1
 	grep -iE "device|trace|rays|frame" $out/${tag}_engine_scene6_4k_${g}gpu.log | head -14
 	sha256sum $out/${tag}_engine_$g.tif; rm -f $out/${tag}_engine_$g.tif
