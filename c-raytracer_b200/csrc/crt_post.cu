@@ -317,6 +317,34 @@ int run_pointwise(float *d_raster, const float *d_z, size_t pixels, const PointO
 
 } // namespace
 
+/* ---- crt_postprocess_device_noalloc: the depth-of-field scratch as a fixed device array -----------
+ * Every device that loads the library holds these CRT_POST_NOALLOC_SCRATCH_BYTES until the process
+ * exits.  Host code must not pass the array's name to a kernel (on the host it is only a stand-in
+ * for the symbol): noalloc_scratch() asks the runtime for its device address, once per device. */
+static __device__ __align__(256) unsigned char g_post_noalloc_scratch[CRT_POST_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+void *g_noalloc_ptr[kMaxDevices];
+std::mutex g_noalloc_mutex;
+
+/* `device` is current (api_ensure_device) */
+int noalloc_scratch(int device, void **out)
+{
+	std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+	if (!g_noalloc_ptr[device]) {
+		void *p = nullptr;
+		POST_TRY(cudaGetSymbolAddress(&p, g_post_noalloc_scratch));
+		if (!p)
+			return api_fail(CRT_ERR_CUDA, "cudaGetSymbolAddress gave no address for the static scratch on device %d", device);
+		g_noalloc_ptr[device] = p;
+	}
+	*out = g_noalloc_ptr[device];
+	return CRT_OK;
+}
+
+} // namespace
+
 extern "C" {
 
 int crt_postprocess_device(int device, const crt_post_opts *opts, uint32_t width, uint32_t height,
@@ -472,6 +500,88 @@ int crt_postprocess(int device, const crt_post_opts *opts, uint32_t width, uint3
 	st.total_ms = ms;
 	if (stats)
 		*stats = st;
+	return CRT_OK;
+}
+
+
+/* The depth-of-field path of crt_postprocess_device() (same kernels, same order, same bits) with its
+ * scratch in g_post_noalloc_scratch: no cudaMalloc / cudaFree / event creation, nothing kept per call.
+ * The array is shared by every call on the device and keeps the last call's contents; the per-row and
+ * per-frame radius maxima are the only part that must start at zero and are cleared on `stream` first.
+ * Calls that overlap on the GPU (different streams without an ordering between them) race on it. */
+int crt_postprocess_device_noalloc(int device, const crt_post_opts *opts, uint32_t width, uint32_t height,
+	float *d_raster, const float *d_z, void *cuda_stream)
+{
+	if (!opts || !d_raster || !d_z)
+		return api_fail(CRT_ERR_INVALID, "NULL argument");
+	if (width == 0 || height == 0)
+		return api_fail(CRT_ERR_INVALID, "empty frame %ux%u", width, height);
+	if (opts->ops & ~(uint32_t)(CRT_POST_BRIGHTEN | CRT_POST_DOF | CRT_POST_DOF_CAMERA | CRT_POST_MIST))
+		return api_fail(CRT_ERR_INVALID, "unknown post-processing operation bits 0x%x", opts->ops);
+	if (!(opts->ops & CRT_POST_DOF))
+		return api_fail(CRT_ERR_INVALID, "crt_postprocess_device_noalloc is the depth-of-field path: CRT_POST_DOF (explicit scale and bias) "
+			"must be set; the other operations need no scratch, use crt_postprocess_device");
+	if ((opts->ops & CRT_POST_MIST) && opts->mist_falloff > CRT_FALLOFF_INV_QUADRATIC)
+		return api_fail(CRT_ERR_INVALID, "unrecognized falloff type %u", opts->mist_falloff);
+	if (device < 0 || device >= kMaxDevices)
+		return api_fail(CRT_ERR_UNSUPPORTED, "device ordinal %d", device);
+	const uint64_t pixels = (uint64_t)width * height;
+	const uint64_t nseg = ((uint64_t)width + kSeg - 1) / kSeg;
+	if (pixels > CRT_POST_NOALLOC_MAX_PIXELS)
+		return api_fail(CRT_ERR_UNSUPPORTED, "frame %ux%u = %llu pixels exceeds the static scratch's limit of %u pixels (CRT_POST_NOALLOC_MAX_PIXELS); "
+			"use crt_postprocess_device", width, height, (unsigned long long)pixels, (unsigned)CRT_POST_NOALLOC_MAX_PIXELS);
+	const size_t src_bytes = align_up((size_t)pixels * sizeof(float4)), radius_bytes = align_up((size_t)pixels * sizeof(uint16_t));
+	const size_t seg_bytes = align_up((size_t)(nseg * height) * sizeof(uint16_t)), rows_bytes = align_up(((size_t)height + 1) * sizeof(int));
+	const size_t need = src_bytes + radius_bytes + seg_bytes + rows_bytes;
+	if (need > (size_t)CRT_POST_NOALLOC_SCRATCH_BYTES)
+		return api_fail(CRT_ERR_UNSUPPORTED, "frame %ux%u needs %zu bytes of scratch, the static array has %zu (CRT_POST_NOALLOC_SCRATCH_BYTES); "
+			"use crt_postprocess_device", width, height, need, (size_t)CRT_POST_NOALLOC_SCRATCH_BYTES);
+	int rc = api_ensure_device(device);
+	if (rc)
+		return rc;
+	void *base = nullptr;
+	rc = noalloc_scratch(device, &base);
+	if (rc)
+		return rc;
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+
+	PointOps after{};
+	after.mist = (opts->ops & CRT_POST_MIST) ? 1u : 0u;
+	after.falloff = opts->mist_falloff;
+	after.start = opts->mist_start;
+	after.inv_depth = 1.f / opts->mist_depth;
+	after.cr = opts->mist_color[0];
+	after.cg = opts->mist_color[1];
+	after.cb = opts->mist_color[2];
+	DofParams p{};
+	p.w = width;
+	p.h = height;
+	p.nseg = (uint32_t)nseg;
+	p.scale = opts->dof_scale;
+	p.bias = opts->dof_bias;
+	p.brighten = (opts->ops & CRT_POST_BRIGHTEN) ? 1u : 0u;
+	p.factor = opts->brighten;
+
+	char *cursor = static_cast<char *>(base);
+	float4 *src = reinterpret_cast<float4 *>(cursor);
+	cursor += src_bytes;
+	uint16_t *radius = reinterpret_cast<uint16_t *>(cursor);
+	cursor += radius_bytes;
+	uint16_t *seg = reinterpret_cast<uint16_t *>(cursor);
+	cursor += seg_bytes;
+	int *row_rmax = reinterpret_cast<int *>(cursor), *frame_rmax = row_rmax + height;
+	POST_TRY(cudaMemsetAsync(row_rmax, 0, ((size_t)height + 1) * sizeof(int), stream));
+	const dim3 block(kSeg, kRows), grid(p.nseg, (height + kRows - 1) / kRows);
+	dof_prepare_kernel<<<grid, block, 0, stream>>>(d_raster, d_z, p, src, radius, seg, row_rmax, frame_rmax);
+	POST_TRY(cudaGetLastError());
+	int rmax = 0;
+	POST_TRY(cudaMemcpyAsync(&rmax, frame_rmax, sizeof rmax, cudaMemcpyDeviceToHost, stream));
+	POST_TRY(cudaStreamSynchronize(stream));
+	if (rmax >= kMaxRadius)
+		return api_fail(CRT_ERR_UNSUPPORTED, "depth of field: a circle of confusion of %d pixels or more (scale %g, bias %g)", kMaxRadius,
+			(double)p.scale, (double)p.bias);
+	dof_gather_kernel<<<grid, block, 0, stream>>>(d_raster, d_z, p, src, radius, seg, row_rmax, frame_rmax, after);
+	POST_TRY(cudaGetLastError());
 	return CRT_OK;
 }
 

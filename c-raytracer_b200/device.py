@@ -22,7 +22,7 @@ SYMBOLS = [
     "crt_shared_alloc", "crt_shared_open", "crt_shared_release", "crt_host_register", "crt_host_unregister", "crt_scene_read_tree",
     "crt_multi_create", "crt_multi_destroy", "crt_multi_num_devices", "crt_multi_is_dynamic", "crt_multi_get_info", "crt_multi_render",
     "crt_trace_closest", "crt_trace_shadow", "crt_texture_eval", "crt_measure_fp32_peak",
-    "crt_postprocess", "crt_postprocess_device",
+    "crt_postprocess", "crt_postprocess_device", "crt_postprocess_device_noalloc",
 ]
 
 _lib = None
@@ -69,6 +69,7 @@ def lib():
         L.crt_postprocess.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
         L.crt_postprocess_device.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_void_p]
+        L.crt_postprocess_device_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -105,6 +106,16 @@ def postprocess_device(opts, width, height, d_raster_ptr, d_z_ptr, device=0, str
     _check(lib().crt_postprocess_device(device, C.addressof(opts), width, height, C.c_void_p(d_raster_ptr), C.c_void_p(d_z_ptr),
                                         C.c_void_p(stream) if stream else None,
                                         C.addressof(stats) if stats is not None else None))
+
+
+def postprocess_device_noalloc(opts, width, height, d_raster_ptr, d_z_ptr, device=0, stream=None):
+    """crt_postprocess_device_noalloc: the depth-of-field path on device pointers with the library's fixed
+    scratch array (no allocation inside the call; frames up to NOALLOC_MAX_PIXELS)."""
+    _check(lib().crt_postprocess_device_noalloc(device, C.addressof(opts), width, height, C.c_void_p(d_raster_ptr),
+                                                C.c_void_p(d_z_ptr), C.c_void_p(stream) if stream else None))
+
+
+NOALLOC_MAX_PIXELS = 1 << 21  # CRT_POST_NOALLOC_MAX_PIXELS
 
 
 class DeviceScene:

@@ -401,6 +401,27 @@ int crt_postprocess(int device, const crt_post_opts *opts, uint32_t width, uint3
 int crt_postprocess_device(int device, const crt_post_opts *opts, uint32_t width, uint32_t height,
 	float *d_raster, const float *d_z_buffer, void *cuda_stream, crt_post_stats *stats);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that
+ * must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  The depth-of-field path of crt_postprocess_device() -- CRT_POST_DOF must be set,
+ * CRT_POST_BRIGHTEN / CRT_POST_MIST may be, CRT_POST_DOF_CAMERA is ignored as there -- with the
+ * same kernels and bit-identical output, but its scratch (per-pixel weighted colours and radii,
+ * per-segment and per-row radius maxima) lives in ONE fixed device array of
+ * CRT_POST_NOALLOC_SCRATCH_BYTES inside the library, which every GPU that loads libcrt.so holds
+ * until the process exits.  The call makes no cudaMalloc / cudaFree / event or stream creation and
+ * keeps nothing per call; inputs and outputs are the caller's device pointers, as above.
+ * Limits: width * height <= CRT_POST_NOALLOC_MAX_PIXELS (1920x1080 fits) and
+ * 18 bytes per pixel + 2 per 32-pixel row segment + 4 per row <= CRT_POST_NOALLOC_SCRATCH_BYTES;
+ * larger frames are refused with CRT_ERR_UNSUPPORTED and a message naming the limit.
+ * The array is shared by all calls on a device and keeps the last call's contents (the call
+ * clears the part that must start at zero): calls that overlap on the GPU -- different streams
+ * with no ordering between them -- race on it; calls on one stream are safe.  Like the existing
+ * path it waits for `cuda_stream` once (the largest radius is checked on the host). */
+#define CRT_POST_NOALLOC_MAX_PIXELS (1u << 21)
+#define CRT_POST_NOALLOC_SCRATCH_BYTES (37u << 20)
+int crt_postprocess_device_noalloc(int device, const crt_post_opts *opts, uint32_t width, uint32_t height,
+	float *d_raster, const float *d_z_buffer, void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif
