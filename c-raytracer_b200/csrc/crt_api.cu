@@ -274,6 +274,64 @@ static int build_host_scene(const crt_scene_desc *desc, HostScene &h)
 		}
 	}
 
+	/* ---- per emitter: the box of all other bounded objects (DEmitter.rest_lo / rest_hi) ------- */
+	if (!h.emitters.empty()) {
+		struct Box {
+			float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+			void add(const crt_object &o)
+			{
+				for (int a = 0; a < 3; a++) {
+					float l, u;
+					if (o.type == CRT_OBJ_SPHERE) {
+						l = o.a[a] - std::fabs(o.b[0]);
+						u = o.a[a] + std::fabs(o.b[0]);
+					} else {
+						const float p0 = o.a[a], p1 = o.a[a] + o.b[a], p2 = o.a[a] + o.c[a];
+						l = std::fmin(p0, std::fmin(p1, p2));
+						u = std::fmax(p0, std::fmax(p1, p2));
+					}
+					lo[a] = std::fmin(lo[a], l);
+					hi[a] = std::fmax(hi[a], u);
+				}
+			}
+		};
+		/* rest(e) = (bounded objects before e) U (bounded objects after e): one pass each way */
+		std::vector<Box> before(h.emitters.size()), after(h.emitters.size());
+		Box run;
+		size_t e = 0;
+		for (size_t k = 0; k < bounded.size(); k++) {
+			if (e < h.emitters.size() && h.emitters[e].object == static_cast<int32_t>(bounded[k]))
+				before[e++] = run;
+			run.add(desc->objects[bounded[k]]);
+		}
+		run = Box();
+		e = h.emitters.size();
+		for (size_t k = bounded.size(); k-- > 0;) {
+			if (e > 0 && h.emitters[e - 1].object == static_cast<int32_t>(bounded[k]))
+				after[--e] = run;
+			run.add(desc->objects[bounded[k]]);
+		}
+		for (size_t i = 0; i < h.emitters.size(); i++) {
+			DEmitter &em = h.emitters[i];
+			for (int a = 0; a < 3; a++) {
+				const float l = std::fmin(before[i].lo[a], after[i].lo[a]), u = std::fmax(before[i].hi[a], after[i].hi[a]);
+				if (!(l <= u)) { /* nothing else is bounded (or a NaN coordinate: then never cull) */
+					em.rest_lo[a] = l == l && u == u ? 1.f : -FLT_MAX;
+					em.rest_hi[a] = l == l && u == u ? -1.f : FLT_MAX;
+					continue;
+				}
+				/* padded like the tree's own boxes, and by the largest epsilon-free margin a hit test could need */
+				const float pad = 1e-5f * std::fmax(1e-3f, std::fmax(std::fabs(l), std::fabs(u))) + 1e-5f * (u - l);
+				em.rest_lo[a] = l - pad;
+				em.rest_hi[a] = u + pad;
+			}
+			if (em.rest_lo[0] > em.rest_hi[0] || em.rest_lo[1] > em.rest_hi[1] || em.rest_lo[2] > em.rest_hi[2]) {
+				em.rest_lo[0] = 1.f; /* the device tests axis 0 for "empty" */
+				em.rest_hi[0] = -1.f;
+			}
+		}
+	}
+
 	/* ---- BVH over the bounded objects ------------------------------------- */
 	const double t0 = now_ms();
 	h.device_build = desc->build == CRT_BUILD_DEVICE;

@@ -48,7 +48,9 @@ struct DEmitter {
 	uint32_t num_lights;
 	uint32_t first_light; /* prefix sum of num_lights over preceding emitters */
 	int32_t is_sphere;
-	int32_t pad;
+	/* box of every OTHER bounded object (padded; lo > hi: there is none).  The sampled emitter never occludes its own
+	 * shadow rays (accel.c:367), so a ray that misses this box cannot be blocked or tinted by the tree and does not walk it */
+	float rest_lo[3], rest_hi[3];
 };
 
 struct DScene {
@@ -278,6 +280,28 @@ __device__ __forceinline__ WideRay make_wide_ray(const Ray &r)
 	const float cx = fminf(fmaxf(w.inx * sc, -big), big), cy = fminf(fmaxf(w.iny * sc, -big), big), cz = fminf(fmaxf(w.inz * sc, -big), big);
 	w.hx = pack_half2(cx, cx); w.hy = pack_half2(cy, cy); w.hz = pack_half2(cz, cz);
 	return w;
+}
+
+#ifndef CRT_REST_BOX
+#define CRT_REST_BOX 1 /* 0: every shadow ray walks the tree from the root (experiments) */
+#endif
+
+/* Can the segment [0, dist] of the ray be shown to miss the box [lo, hi]?  FP32 slab test in units of tau = t * maxd
+ * with the ray's safe reciprocals; margins of 1e-5 relative (the products carry a few ulp) on a box the host padded.
+ * Written so that a NaN anywhere answers false (the ray then walks the tree as before). */
+__device__ __forceinline__ bool ray_misses_box(const float *lo, const float *hi, const Ray &r, const WideRay &w, float dist)
+{
+	const float lx = __ldg(lo), ly = __ldg(lo + 1), lz = __ldg(lo + 2), ux = __ldg(hi), uy = __ldg(hi + 1), uz = __ldg(hi + 2);
+	if (lx > ux)
+		return true; /* no other bounded object */
+	const float ax = (lx - r.ox) * w.inx, bx = (ux - r.ox) * w.inx;
+	const float ay = (ly - r.oy) * w.iny, by = (uy - r.oy) * w.iny;
+	const float az = (lz - r.oz) * w.inz, bz = (uz - r.oz) * w.inz;
+	const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+	const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+	const float lim = dist * w.maxd;
+	const float slack = fmaf(fabsf(tn) + fabsf(tf), 1e-5f, 1e-30f);
+	return tn - tf > slack || tf < -slack || tn > fmaf(fabsf(lim), 1e-5f, lim) + slack;
 }
 
 struct alignas(32) Vec8 {

@@ -535,6 +535,13 @@ __global__ void __launch_bounds__(kBlockThreads, CRT_MIN_BLOCKS) render_kernel(c
 									blocked = shadow_planes<COUNT>(sc, sr, dist, ir, ig, ib, cn);
 									if (!blocked && sc.num_nodes != 0u) {
 										rw = make_wide_ray(sr);
+#if CRT_REST_BOX
+										/* most rays of an open scene pass the other objects' box by: decided here, with
+										 * all fetching lanes in step, instead of by a NODE and a PRIM step of the walk
+										 * (the emitter's own primitive) */
+										Cnt<COUNT>::add(cn.box);
+										if (!ray_misses_box(em.rest_lo, em.rest_hi, sr, rw, dist))
+#endif
 										sw.inner = 1u; /* the root of the wide tree; both stacks are empty */
 									}
 								}
