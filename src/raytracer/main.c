@@ -52,7 +52,59 @@ static const char *const HELP_EXTRA =
 	"[--fog] (decimal)                : DEFAULT = 0       : in-tracer fog: extinction per unit length along every eye-path segment.\n"
 	"[--fog-color] (r,g,b)            : DEFAULT = 0,0,0   : in-tracer fog: colour gained where light is lost.\n"
 	"[--seed] (integer)               : DEFAULT = 1       : seed of the counter-based sampling stream.\n"
-	"[--stats]                        : DEFAULT = OFF     : count rays and intersection tests, print Mrays/s.\n";
+	"[--stats]                        : DEFAULT = OFF     : count rays and intersection tests, print Mrays/s.\n"
+	"[--stats-json] (string)          : DEFAULT = none    : file the same counters are written to as JSON (rays by class, tests, ms, Mrays/s, FP32 roofline fraction).\n";
+
+/* --stats-json: the counters of the frame, machine readable.  Algorithmic FLOPs by the constants of the scope contract
+ * (3 per ray, 12 per box test, triangle 14 / 24 / 40 / 46 by exit stage, sphere 17 / 20, plane 12); the peak is the FFMA
+ * rate measured on the same device (crt_measure_fp32_peak). */
+static int write_stats_json(const char *path, const char *scene_file, const crt_render_opts *o, const crt_stats *st,
+	const crt_scene_info *info, const int *devices, const double *device_ms, int num_devices, int dynamic)
+{
+	FILE *f = fopen(path, "w");
+	if (!f)
+		return 1;
+	const double rays = (double)(st->rays_closest + st->rays_shadow);
+	const double flops = 3.0 * rays + 12.0 * (double)st->box_tests + 14.0 * (double)st->tri_tests[0] + 24.0 * (double)st->tri_tests[1] +
+		40.0 * (double)st->tri_tests[2] + 46.0 * (double)st->tri_tests[3] + 17.0 * (double)st->sphere_tests[0] +
+		20.0 * (double)st->sphere_tests[1] + 12.0 * (double)st->plane_tests;
+	double peak = 0.0;
+	if (crt_measure_fp32_peak((int)info->device, &peak) != CRT_OK)
+		peak = 0.0;
+	const double tflops = st->kernel_ms > 0.0 ? flops / (st->kernel_ms * 1e9) : 0.0;
+	fprintf(f, "{\"scene\": \"");
+	for (const char *c = scene_file; *c; c++) { /* a path: escape the two characters JSON cannot take raw */
+		if (*c == '"' || *c == '\\')
+			fputc('\\', f);
+		fputc(*c, f);
+	}
+	fprintf(f, "\", \"width\": %u, \"height\": %u, \"samples_per_pixel\": %u, \"seed\": %u,\n", o->width, o->height, o->samples_per_pixel, o->seed);
+	fprintf(f, " \"rays_closest\": %llu, \"rays_shadow\": %llu, \"nodes_shaded\": %llu,\n", (unsigned long long)st->rays_closest,
+		(unsigned long long)st->rays_shadow, (unsigned long long)st->nodes_shaded);
+	fprintf(f, " \"box_tests\": %llu, \"tri_tests\": [%llu, %llu, %llu, %llu], \"sphere_tests\": [%llu, %llu], \"plane_tests\": %llu,\n",
+		(unsigned long long)st->box_tests, (unsigned long long)st->tri_tests[0], (unsigned long long)st->tri_tests[1],
+		(unsigned long long)st->tri_tests[2], (unsigned long long)st->tri_tests[3], (unsigned long long)st->sphere_tests[0],
+		(unsigned long long)st->sphere_tests[1], (unsigned long long)st->plane_tests);
+	fprintf(f, " \"node_steps\": %llu, \"node_step_lanes\": %llu, \"node_step_idle\": %llu, \"prim_steps\": %llu, \"prim_step_lanes\": %llu, \"prim_step_idle\": %llu,\n",
+		(unsigned long long)st->node_steps, (unsigned long long)st->node_step_lanes, (unsigned long long)st->node_step_idle,
+		(unsigned long long)st->prim_steps, (unsigned long long)st->prim_step_lanes, (unsigned long long)st->prim_step_idle);
+	fprintf(f, " \"kernel_ms\": %.6f, \"total_ms\": %.6f, \"queue_ms\": %.6f, \"last_warp_ms\": %.6f, \"warp_busy_ms\": %.6f,\n", st->kernel_ms,
+		st->total_ms, st->queue_ms, st->last_warp_ms, st->warp_busy_ms);
+	fprintf(f, " \"mrays_per_s\": %.6f, \"box_tests_per_ray\": %.6f, \"flops\": %.0f, \"flops_per_ray\": %.6f,\n",
+		st->kernel_ms > 0.0 ? rays / (st->kernel_ms * 1e3) : 0.0, rays > 0.0 ? (double)st->box_tests / rays : 0.0, flops,
+		rays > 0.0 ? flops / rays : 0.0);
+	fprintf(f, " \"roofline\": {\"bound\": \"fp32\", \"achieved\": %.6f, \"peak\": %.6f, \"unit\": \"TFLOP/s\", \"frac\": %.6f, \"note\": \"kernel_ms is the instrumented instance's (slower than the plain one)\"},\n",
+		tflops, peak, peak > 0.0 ? tflops / peak : 0.0);
+	fprintf(f, " \"bvh\": {\"nodes\": %u, \"primitives\": %u, \"planes\": %u, \"depth\": %u, \"built_on\": \"%s\", \"build_ms\": %.6f, \"upload_ms\": %.6f, \"device_bytes\": %llu},\n",
+		info->num_nodes, info->num_bounded, info->num_planes, info->max_depth, info->built_on_device ? "device" : "host", info->build_ms,
+		info->upload_ms, (unsigned long long)info->device_bytes);
+	fprintf(f, " \"emitters\": %u, \"light_samples\": %u, \"sm_count\": %u,\n", info->num_emitters, info->total_lights, info->sm_count);
+	fprintf(f, " \"devices\": [");
+	for (int k = 0; k < num_devices; k++)
+		fprintf(f, "%s{\"device\": %d, \"kernel_ms\": %.6f}", k ? ", " : "", devices[k], device_ms[k]);
+	fprintf(f, "], \"work_queue\": \"%s\"}\n", num_devices > 1 ? (dynamic ? "shared" : "static shards") : "single device");
+	return fclose(f) != 0;
+}
 
 int main(int argc, char *argv[])
 {
@@ -120,9 +172,9 @@ int main(int argc, char *argv[])
 	rt_log("Commencing raytracing.");
 	crt_stats stats;
 	crt_scene_info info;
+	double device_ms[64];
+	int dynamic = 0;
 	if (num_devices > 1) {
-		double device_ms[64];
-		int dynamic = 0;
 		rt_log("Using %d CUDA devices.", num_devices);
 		if (rt_render_multi(&scene, &image, &opts, devices, num_devices, &stats, &info, device_ms, &dynamic, err))
 			rt_fatal("%s", err);
@@ -138,6 +190,16 @@ int main(int argc, char *argv[])
 		rt_log("Rays: %llu closest-hit + %llu shadow = %.1f Mrays/s; %.1f box tests per ray.",
 			(unsigned long long)stats.rays_closest, (unsigned long long)stats.rays_shadow,
 			rays / (stats.kernel_ms * 1e3), rays > 0 ? (double)stats.box_tests / rays : 0.0);
+	}
+	const int sj = rt_args_find_with_values(&args, "--stats-json", 1);
+	if (sj) {
+		if (num_devices <= 1) {
+			devices[0] = num_devices == 1 ? devices[0] : device;
+			device_ms[0] = stats.kernel_ms;
+		}
+		if (write_stats_json(argv[sj + 1], argv[RT_ARG_SCENE], &opts, &stats, &info, devices, device_ms, num_devices > 1 ? num_devices : 1, dynamic))
+			rt_fatal("Failed to write statistics to [%s].", argv[sj + 1]);
+		rt_log("Statistics written to [%s].", argv[sj + 1]);
 	}
 
 	rt_log("Saving image.");

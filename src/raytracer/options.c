@@ -69,7 +69,7 @@ void rt_render_parse(crt_render_opts *o, const struct rt_args *args)
 		o->attenuation_offset = (float)atof(v);
 	if ((v = value_of(args, "--seed")))
 		o->seed = (uint32_t)strtoul(v, NULL, 10);
-	if (rt_args_find(args, "--stats"))
+	if (rt_args_find(args, "--stats") || rt_args_find_with_values(args, "--stats-json", 1))
 		o->flags |= CRT_RENDER_COUNT_STATS;
 	/* extensions without a counterpart in the reference (include/crt.h): off unless asked for */
 	if ((v = value_of(args, "--lens-radius")))

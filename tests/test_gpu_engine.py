@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 from _util import ROOT
-from c_raytracer_b200 import device, host
+from c_raytracer_b200 import _abi, device, host
 
 pytestmark = pytest.mark.gpu
 
@@ -66,3 +66,34 @@ def test_engine_reports_missing_device_flag(tmp_path):
     out = subprocess.run([exe, "scenes/scene1.json", str(tmp_path / "o.tif"), "8", "8", "--device", "99"],
                          capture_output=True, text=True, cwd=ROOT)
     assert out.returncode == 1 and "device" in out.stdout.lower()
+
+
+def test_engine_stats_json(tmp_path):
+    """--stats-json: the counters of the frame as JSON; they equal the library's own for the same options."""
+    import json
+    if device.device_count() < 1:
+        pytest.fail("no CUDA device")
+    w, h = 96, 54
+    flags = ["-g", "path", "-n", "2", "--seed", "3"]
+    p, j = str(tmp_path / "out.tif"), str(tmp_path / "stats.json")
+    log = _run_engine(["scenes/scene4.json", p, str(w), str(h), "--stats-json", j] + flags)
+    assert "Statistics written" in log and "Rays:" in log  # --stats-json implies the counted kernel instance
+    d = json.load(open(j))
+    sc = host.Scene(os.path.join(ROOT, "scenes", "scene4.json"))
+    o = sc.options(w, h, *flags)
+    o.flags |= _abi.CRT_RENDER_COUNT_STATS
+    st = _abi.Stats()
+    dev = device.DeviceScene(sc, 0)
+    dev.render(o, st)
+    assert (d["width"], d["height"], d["samples_per_pixel"], d["seed"]) == (w, h, 2, 3)
+    assert (d["rays_closest"], d["rays_shadow"], d["box_tests"], d["plane_tests"]) == (st.rays_closest, st.rays_shadow, st.box_tests, st.plane_tests)
+    assert d["tri_tests"] == list(st.tri_tests) and d["sphere_tests"] == list(st.sphere_tests)
+    assert d["flops"] == pytest.approx(_abi.algorithmic_flops(st), rel=1e-12)
+    rays = st.rays_closest + st.rays_shadow
+    assert d["mrays_per_s"] == pytest.approx(rays / (d["kernel_ms"] * 1e3), rel=1e-5)
+    assert d["box_tests_per_ray"] == pytest.approx(st.box_tests / rays, rel=1e-5)
+    r = d["roofline"]
+    assert r["bound"] == "fp32" and 30.0 < r["peak"] < 90.0 and 0.0 < r["frac"] < 1.0
+    assert r["frac"] == pytest.approx(r["achieved"] / r["peak"], abs=2e-6)
+    assert d["bvh"]["nodes"] == dev.info.num_nodes and d["bvh"]["primitives"] == dev.info.num_bounded and d["bvh"]["built_on"] == "host"
+    assert d["devices"] == [{"device": 0, "kernel_ms": d["kernel_ms"]}] and d["work_queue"] == "single device"
