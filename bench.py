@@ -398,7 +398,9 @@ def ours(a):
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "dram_traffic.json")))
         # only the capture of THESE device sources on THIS workload counts (libcrt.so is not reproducible bit for bit)
-        if t["workload"] == workload_name(a) and world == t["n_gpus"] and not info.built_on_device and t.get("device_sources_sha256") == device.source_fingerprint():
+        # ... or of sources recorded there as compiling to the same device code (host-only changes; the entry says how that was checked)
+        same = [t.get("device_sources_sha256")] + [e.get("device_sources_sha256") for e in t.get("same_device_code", [])]
+        if t["workload"] == workload_name(a) and world == t["n_gpus"] and not info.built_on_device and device.source_fingerprint() in same:
             traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     except (OSError, KeyError, ValueError):
         pass

@@ -474,6 +474,7 @@ void plan_collapse(WideBuilder &W)
 		float *cost = &W.cost[7 * v];
 		uint8_t *split = &W.split[8 * v];
 		float best = FLT_MAX;
+		split[0] = 4; /* any share 1..7 is a valid collapse: kept when no cost below compares smaller (surfaces that overflow, NaN boxes) */
 		for (int k = 1; k <= 7; k++) {
 			const float c = forest_cost(W, ref[0], cbox[0], k) + forest_cost(W, ref[1], cbox[1], 8 - k);
 			if (c < best) {
@@ -539,8 +540,9 @@ void quantize_node(WideNode &n, const std::vector<WideRef> &kids, const std::vec
 		e = std::min(std::max(ex, -40), 40);
 	}
 	double scale = std::ldexp(1.0, e);
-	/* a scale clamped from above cannot hold the node: widen until it does (boxes that large are not built in practice) */
-	while (extent > (kWideGrid - 1.0) * scale) {
+	/* a scale clamped from above cannot hold the node: widen until it does (boxes that large are not built in practice;
+	 * the exponent byte ends at 2^127, which also ends the loop for an infinite extent) */
+	while (extent > (kWideGrid - 1.0) * scale && e < 127) {
 		e++;
 		scale = std::ldexp(1.0, e);
 	}

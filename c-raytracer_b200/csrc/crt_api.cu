@@ -111,6 +111,8 @@ int upload(crt_scene *s, const std::vector<T> &host, const T **dev)
 	return CRT_OK;
 }
 
+constexpr float kMaxCoordinate = 1e12f;
+
 int validate(const crt_scene_desc *desc)
 {
 	if (!desc)
@@ -129,6 +131,14 @@ int validate(const crt_scene_desc *desc)
 			return fail(CRT_ERR_INVALID, "object %u has unknown type %d", i, o.type);
 		if (o.material < 0 || static_cast<uint32_t>(o.material) >= desc->num_materials)
 			return fail(CRT_ERR_INVALID, "object %u references material index %d of %u", i, o.material, desc->num_materials);
+		/* the tree builders form surface areas and Morton codes in FP32: coordinates must be finite and leave room for
+		 * their squares (a = centre / vertex / normal, b, c = radius / edges / plane offset) */
+		for (int k = 0; k < 3; k++) {
+			const float v[3] = { o.a[k], o.b[k], o.c[k] };
+			for (int j = 0; j < (o.type == CRT_OBJ_TRIANGLE ? 3 : (k == 0 ? 2 : 1)); j++)
+				if (!(std::fabs(v[j]) <= kMaxCoordinate))
+					return fail(CRT_ERR_UNSUPPORTED, "object %u has a coordinate that is not finite or beyond %g", i, (double)kMaxCoordinate);
+		}
 	}
 	return CRT_OK;
 }

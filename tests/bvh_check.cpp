@@ -1,6 +1,7 @@
 /* bvh_check -- invariants of the host tree builders (c-raytracer_b200/csrc/bvh_build.cpp),
  * run by tests/test_bvh_build.py on seeded boxes:
- *   bvh_check <n> <seed> <kind>      kind 0: uniform cloud, 1: flat axis-aligned sheets, 2: many coincident boxes
+ *   bvh_check <n> <seed> <kind>      kind 0: uniform cloud, 1: flat axis-aligned sheets, 2: many coincident boxes,
+ *                                    3: exponential chain (deep tree), 4: the same up to 10^30 (surfaces overflow FP32)
  * Exits 0 and prints a summary line, or prints the violated invariant and exits 1. */
 #include <cmath>
 #include <cstdio>
@@ -48,6 +49,15 @@ int main(int argc, char **argv)
 				c = 1.5f, s = 0.01f; /* three quarters of the boxes coincide */
 			boxes[i].lo[k] = c - s;
 			boxes[i].hi[k] = c + s;
+		}
+		if (kind == 3 || kind == 4) {
+			/* exponential chain: SAH peels the largest box off at every level, the wide tree gets deeper than the
+			 * walk's shared-memory stack (kind 3, coordinates <= 10^6); kind 4 grows until the FP32 surfaces overflow */
+			const double c = 1e-6 * std::pow(kind == 3 ? 1.2 : 2.0, (double)(i % (kind == 3 ? 150u : 120u))), r = 0.2 * c;
+			for (int k = 0; k < 3; k++) {
+				boxes[i].lo[k] = (float)(c - r);
+				boxes[i].hi[k] = (float)(c + r);
+			}
 		}
 	}
 
@@ -143,7 +153,7 @@ int main(int argc, char **argv)
 		CHECK(lmask == (1u << nl) - 1u && imask == (((1u << ni) - 1u) << nl) && nl + ni >= 1 && nl + ni <= 8,
 			"slots of wide node %d are not leaves-then-inner (masks %02x %02x)", it.node, lmask, imask);
 		const int e = (int)(wn.meta & 0xffu) - 127;
-		CHECK(e >= -40 && e <= 60, "grid exponent %d of node %d out of range", e, it.node);
+		CHECK(e >= -40 && e <= (kind == 4 ? 127 : 60), "grid exponent %d of node %d out of range", e, it.node);
 		const double scale = std::ldexp(1.0, e);
 		for (int j = 0; j < 8; j++) {
 			const bool used = ((lmask | imask) >> j) & 1u;

@@ -66,3 +66,42 @@ def test_product_does_not_reference_oracle():
     # crt_rng.h documents the shared stream and mentions the shim's file name only in a comment
     bad = [b for b in bad if not b.endswith("crt_rng.h")]
     assert not bad, bad
+
+
+def test_scene_coordinates_are_validated_before_any_device_work():
+    """crt_scene_create refuses non-finite or huge coordinates (the tree builders form FP32 surfaces and Morton codes;
+    surfaces that overflowed once overran a stack buffer in the 8-wide collapse): checked on the host, so the
+    answer is the same with and without a GPU."""
+    import ctypes as C
+
+    import numpy as np
+    if not os.path.exists(device.LIB_PATH):
+        pytest.skip("libcrt.so not built")
+    sc = host.Scene(scene_path("scene1"))
+    objs = np.array(sc.objects)  # a copy of the 64-byte records
+    for field, value in (("a", 1e13), ("a", np.inf), ("b", np.nan), ("a", -3e38)):
+        bad = objs.copy()
+        k = int(np.flatnonzero(bad["type"] == _abi.CRT_OBJ_SPHERE)[0])
+        bad[field][k, 0] = value
+        desc = _abi.SceneDesc.from_buffer_copy(sc.desc)
+        desc.objects = C.cast(bad.ctypes.data, type(desc.objects))
+        h = C.c_void_p()
+        rc = device.lib().crt_scene_create(C.addressof(desc), 0, C.byref(h))
+        assert rc == -5 and h.value is None, (field, value, rc)  # CRT_ERR_UNSUPPORTED
+        assert b"coordinate" in device.lib().crt_last_error()
+
+
+def test_dram_traffic_record_belongs_to_this_build():
+    """profiles/dram_traffic.json (bench.py's roofline.traffic) names the device sources it was captured from, and any
+    later sources that compile to the same device code; the SASS of the library built here is the recorded one."""
+    import hashlib
+    import json
+    import shutil
+    t = json.load(open(os.path.join(ROOT, "profiles", "dram_traffic.json")))
+    same = [t["device_sources_sha256"]] + [e["device_sources_sha256"] for e in t.get("same_device_code", [])]
+    if device.source_fingerprint() not in same:
+        pytest.skip("the device sources changed after the capture: bench.py reports traffic null")
+    if not os.path.exists(device.LIB_PATH) or not shutil.which("cuobjdump"):
+        pytest.skip("libcrt.so or cuobjdump missing")
+    sass = subprocess.run(["cuobjdump", "-sass", device.LIB_PATH], capture_output=True, check=True).stdout
+    assert hashlib.sha256(sass).hexdigest() == t["sass_sha256"]

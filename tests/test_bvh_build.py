@@ -25,6 +25,7 @@ def checker(tmp_path_factory):
 @pytest.mark.parametrize("n,seed,kind", [
     (0, 1, 0), (1, 1, 0), (2, 2, 0), (5, 3, 0), (9, 4, 2), (1000, 5, 0), (1000, 6, 1), (4000, 7, 2),
     (60000, 8, 0), (60000, 9, 1), (150000, 10, 2),
+    (150, 11, 3), (600, 12, 3), (120, 13, 4), (500, 14, 4),  # deep chains; surfaces that overflow FP32 (once a stack overflow in the collapse)
 ])
 def test_tree_invariants(checker, n, seed, kind):
     r = subprocess.run([checker, str(n), str(seed), str(kind)], capture_output=True, text=True)
