@@ -164,6 +164,20 @@ int rt_stl_load(const char *filename, const float position[3], const float rotat
 	}
 	uint32_t n;
 	memcpy(&n, header + STL_HEADER_BYTES, 4);
+	/* the triangle count is the file's own claim: hold it against the file's size before anything is allocated for it */
+	{
+		long size = -1;
+		if (!fseek(f, 0, SEEK_END))
+			size = ftell(f);
+		if (size < 0 || fseek(f, (long)sizeof header, SEEK_SET)) {
+			fclose(f);
+			rt_fail(err, "Failed to read triangle in mesh file [%s].", filename);
+		}
+		if ((uint64_t)n * STL_RECORD_BYTES > (uint64_t)size - sizeof header) {
+			fclose(f);
+			rt_fail(err, "Failed to read triangle in mesh file [%s].", filename);
+		}
+	}
 
 	float rot[3][3];
 	euler_zyx(rot, rotation);

@@ -152,6 +152,29 @@ def test_ascii_stl_rejected(tmp_path):
         host.Scene(_write(tmp_path, s))
 
 
+def test_stl_triangle_count_is_held_against_the_file(tmp_path):
+    """A mesh header may claim any triangle count: truncated files and counts beyond the file are refused before
+    memory is set aside for them (a 134-byte file claiming 2^32 - 1 triangles once asked for 256 GB)."""
+    import struct
+    one = struct.pack("<12fH", 0, 0, 1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0)
+    s = _base_scene()
+    stl = tmp_path / "m.stl"
+    s["Objects"].append({"type": "Mesh", "parameters": {"material": s["Materials"][0]["id"], "filename": str(stl),
+                                                       "position": [0, 0, 0], "rotation": [0, 0, 0], "scale": 1}})
+    for count, body, ok in ((1, one, True), (2, one + one, True), (2, one, False), (0xffffffff, one, False), (0x80000000, one + one, False),
+                            (1, one[:-1], False), (0, b"", True)):
+        stl.write_bytes(b"\0" * 80 + struct.pack("<I", count) + body)
+        if ok:
+            sc = host.Scene(_write(tmp_path, s))
+            assert (sc.objects["type"] == 1).sum() == count
+        else:
+            with pytest.raises(host.SceneError, match="Failed to read triangle in mesh file"):
+                host.Scene(_write(tmp_path, s))
+    stl.write_bytes(b"\0" * 83)
+    with pytest.raises(host.SceneError, match="Failed to read header of mesh file"):
+        host.Scene(_write(tmp_path, s))
+
+
 def test_emitter_without_lights_and_defaults(tmp_path):
     """`lights` absent -> 0 samples; `epsilon` absent -> automatic rules."""
     s = _base_scene()
@@ -328,3 +351,16 @@ def test_bench_goldens_are_complete():
         assert g["raster"].shape == (h, w, 3) and g["z"].shape == (h, w)
         assert 0.01 < float(g["seed_to_seed_rel_rmse"]) < 1.0
         assert len(str(g["mesh_sha256"])) == 64 and int(g["shadow"]) > 0
+
+
+def test_loaders_survive_mutated_inputs(tmp_path):
+    """tools/fuzz: the scene, STL and TIFF loaders built with ASan + UBSan on seeded mutations of the stock inputs
+    (truncations, flipped bytes, extreme numbers, counts beyond the file, deep nesting): a case may be refused, never
+    crash.  A short fixed-seed run here; tools/fuzz/run.sh <seed> <cases> for longer ones."""
+    import shutil
+    if not shutil.which("gcc"):
+        pytest.skip("gcc missing")
+    env = dict(os.environ, CRT_FUZZ_DIR=str(tmp_path))
+    r = subprocess.run(["bash", os.path.join(ROOT, "tools", "fuzz", "run.sh"), "3", "120"], capture_output=True, text=True, env=env, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.stdout.count("bad 0") == 3
